@@ -1,0 +1,163 @@
+/*
+ * nerf_b200.h — C ABI of libnerf_b200.so: the B200 (sm_100a) replacement for the hot path of
+ * elisabeth96/nerf-rs (per-sample NeRF MLP inference + ray marching + compositing over the coarse and
+ * fine lego_rust networks).
+ *
+ * The reference is a pure-Rust crate without any FFI surface; the seam is its Rust API.  Each entry point
+ * below names the reference function it stands in for (file:line into the reference crate).  The Rust
+ * shim a maintainer would add is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - Every function returns NERF_OK (0) or a negative nerf_status; nothing unwinds across the ABI
+ *     (the reference panics: lib.rs:36,118,483-501).  nerf_last_error() gives the message (thread-local).
+ *   - The caller owns every buffer passed in or out.  A nerf_ctx owns device weights, workspaces and
+ *     streams; it is internally serialised and may be used from any host thread.
+ *   - The library is CUDA-only: there is no CPU fallback.  nerf_create fails with NERF_E_CUDA when no
+ *     sm_100 device is present.
+ *   - "host" entry points take host pointers and include H2D/D2H copies; "*_device" entry points take
+ *     device pointers on the context's device and enqueue on `stream` (a cudaStream_t passed as void*),
+ *     returning without synchronising.
+ */
+#ifndef NERF_B200_H
+#define NERF_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  NERF_OK = 0,
+  NERF_E_ARG = -1,   /* bad argument: W%8, H%8, n_coarse==0 (lib.rs:483-501), null pointers, ranges */
+  NERF_E_IO = -2,    /* weight / camera / ppm file could not be read or written (lib.rs:36,65,569) */
+  NERF_E_SHAPE = -3, /* missing tensor or dims mismatch (lib.rs:118,127) */
+  NERF_E_CUDA = -4,  /* CUDA runtime error, or no sm_100 device */
+  NERF_E_UNSUPPORTED = -5
+} nerf_status;
+
+/* Arithmetic of the 256-wide dense layers.  Heads (sigma, rgb), encodings, sampling and compositing are
+ * always f32. */
+typedef enum {
+  NERF_PREC_FP32 = 0, /* CUDA-core path; per-element sum order identical to network.rs:134-143 */
+  NERF_PREC_BF16 = 1, /* tcgen05 kind::f16, bf16 operands, f32 accumulate in TMEM */
+  NERF_PREC_FP16 = 2, /* tcgen05 kind::f16, fp16 operands (tf32-class 10-bit mantissa at bf16 rate) */
+  NERF_PREC_TF32 = 3  /* reserved; currently served by the FP16 path (same operand mantissa) */
+} nerf_precision;
+
+typedef enum { NERF_NET_COARSE = 0, NERF_NET_FINE = 1 } nerf_net_id;
+
+/* The reference draws jitter from an OS-seeded thread_rng (lib.rs:243,332,375,407), which cannot be
+ * reproduced; these are the reproducible substitutes. */
+typedef enum {
+  NERF_SAMPLING_DET = 0,    /* jitter = 0.5, u_k = (k + 0.5) / n_fine */
+  NERF_SAMPLING_PHILOX = 1, /* Philox4x32-10 keyed by (seed, pixel_index, stream) */
+  NERF_SAMPLING_ARRAYS = 2  /* caller supplies the uniforms */
+} nerf_sampling_mode;
+
+typedef struct nerf_ctx nerf_ctx;
+
+/* One named tensor, names and dims as in lego_rust/<net>/shapes.txt (weights.rs:11-95). */
+typedef struct {
+  const char* name;  /* e.g. "dense5_kernel" */
+  int32_t ndim;      /* 2 for kernels [in,out], 1 for biases */
+  int64_t dims[2];
+  const float* data; /* host, row-major f32 */
+} nerf_tensor;
+
+/* struct Camera after camera_from_samples (lib.rs:197-211,614-645). */
+typedef struct {
+  float origin[3];
+  float forward[3]; /* normalised */
+  float up[3];      /* normalised */
+  float alpha_w;    /* atan(0.5*W_ref/focal) */
+  float alpha_h;
+  float near_;
+  float far_;
+} nerf_camera;
+
+typedef struct {
+  int32_t mode; /* nerf_sampling_mode */
+  uint64_t seed;
+  const float* jitter; /* ARRAYS: [ray_end-ray_begin][n_coarse]; host ptr for host calls, device ptr for *_device */
+  const float* u;      /* ARRAYS: [ray_end-ray_begin][n_fine] */
+} nerf_sampling;
+
+/* Optional per-stage outputs of nerf_render_stages (host pointers, any may be NULL), indexed by
+ * pixel_index - ray_begin. */
+typedef struct {
+  float* dirs;    /* [n][3]        normalised ray directions      (lib.rs:214-230,371) */
+  float* t_c;     /* [n][nc]       stratified samples             (lib.rs:233-248) */
+  float* sigma_c; /* [n][nc]       coarse density                 (lib.rs:404) */
+  float* w_c;     /* [n][nc]       coarse weights                 (lib.rs:250-283) */
+  float* t_f;     /* [n][nc+nf]    merged + sorted samples        (lib.rs:416-420) */
+  float* sigma_f; /* [n][nc+nf]    fine density                   (lib.rs:445) */
+  float* rgb_f;   /* [n][nc+nf][3] fine colour */
+} nerf_stages;
+
+/* Timing of the last nerf_render / nerf_forward_batch on a context, from CUDA events (ms). */
+typedef struct {
+  float total_ms;      /* first kernel to last kernel, device time */
+  float mlp_coarse_ms; /* fused MLP kernel, coarse pass */
+  float mlp_fine_ms;   /* fused MLP kernel, fine pass */
+  float sampling_ms;   /* ray generation + stratified + importance sampling kernels */
+  float composite_ms;  /* compositing kernel */
+  int32_t kernel_launches;
+} nerf_timing;
+
+const char* nerf_last_error(void);
+const char* nerf_version(void);
+
+/* load_network_from_dir x2 (lib.rs:108-174, called at lib.rs:651-652): reads <root>/coarse and <root>/fine
+ * (shapes.txt + <name>.bin, little-endian f32), uploads them and builds the pre-swizzled bf16 / fp16
+ * operand tiles.  `device` is a CUDA ordinal. */
+int nerf_create(const char* weights_root, int device, nerf_ctx** out);
+/* Same from caller-held tensors (Network::new, network.rs:181-195). */
+int nerf_create_from_tensors(const nerf_tensor* coarse, int n_coarse, const nerf_tensor* fine, int n_fine, int device,
+                             nerf_ctx** out);
+void nerf_destroy(nerf_ctx*);
+
+/* Network::forward_batch (network.rs:197-237).  points: [3][B] feature-major (the reference's Matrix 3xB),
+ * dirs: [B][3], rgb: [B][3], sigma: [B].  B == 0 is a no-op (network.rs:199-201). */
+int nerf_forward_batch(nerf_ctx*, int net, const float* points, const float* dirs, int64_t B, int precision,
+                       float* rgb, float* sigma);
+int nerf_forward_batch_device(nerf_ctx*, int net, const float* d_points, const float* d_dirs, int64_t B,
+                              int precision, float* d_rgb, float* d_sigma, void* stream);
+
+/* render_image (lib.rs:474-565) restricted to pixel indices [ray_begin, ray_end) (pixel_index = i*W + j,
+ * lib.rs:371); pass 0 and W*H for the whole frame.  rgb: [ray_end-ray_begin][3] f32. */
+int nerf_render(nerf_ctx*, const nerf_camera*, int W, int H, int n_coarse, int n_fine, int precision,
+                const nerf_sampling*, int64_t ray_begin, int64_t ray_end, float* rgb);
+int nerf_render_device(nerf_ctx*, const nerf_camera*, int W, int H, int n_coarse, int n_fine, int precision,
+                       const nerf_sampling*, int64_t ray_begin, int64_t ray_end, float* d_rgb, void* stream);
+/* nerf_render plus the intermediate stages of render_block (lib.rs:353-472). */
+int nerf_render_stages(nerf_ctx*, const nerf_camera*, int W, int H, int n_coarse, int n_fine, int precision,
+                       const nerf_sampling*, int64_t ray_begin, int64_t ray_end, float* rgb, const nerf_stages*);
+
+/* Stage entry points (host buffers), one per reference function, used by the stage-wise parity tests. */
+int nerf_ray_dirs(nerf_ctx*, const nerf_camera*, int W, int H, int64_t ray_begin, int64_t ray_end,
+                  float* dirs /*[n][3]*/);                                   /* lib.rs:214-230 + :371 */
+int nerf_compute_weights(nerf_ctx*, const float* sigma, const float* t, int64_t n_rays, int n, float far_,
+                         float* w);                                          /* lib.rs:250-283 */
+int nerf_sample_importance(nerf_ctx*, const float* t, const float* w, int64_t n_rays, int n, const float* u,
+                           int count, float* t_merged /*[n_rays][n+count] sorted*/); /* lib.rs:289-351,416-420 */
+int nerf_integrate_rays(nerf_ctx*, const float* rgb, const float* sigma, const float* t, int64_t n_rays, int n,
+                        float far_, float* out /*[n_rays][3]*/);             /* lib.rs:176-195 */
+
+int nerf_get_timing(nerf_ctx*, nerf_timing* out);
+
+/* Host-side helpers of the boundary (no GPU needed). */
+/* camera_from_samples (lib.rs:614-645) over the JSON keys near, far, camera_origin, camera_forward,
+ * camera_up, hwf (lib.rs:620-629). */
+int nerf_camera_from_json(const char* path, nerf_camera* out);
+int nerf_camera_from_values(double near_, double far_, const double origin[3], const double forward[3],
+                            const double up[3], const double hwf[3], nerf_camera* out);
+/* save_ppm (lib.rs:567-580): "P6\n{w} {h}\n255\n" + (clamp(v,0,1)*255+0.5) as u8. */
+int nerf_save_ppm(const char* path, int W, int H, const float* rgb);
+/* The same quantiser on a buffer. */
+int nerf_quantize_rgb8(const float* rgb, int64_t n, uint8_t* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NERF_B200_H */

@@ -1,0 +1,667 @@
+// api.cu — the C ABI of libnerf_b200.so (include/nerf_b200.h): context, weight upload, workspaces and the
+// kernel schedule of render_block / render_image (src/lib.rs:353-565).  CUDA-only: no CPU fallback.
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include "common.cuh"
+#include "host_util.h"
+#include "mlp_tc.h"
+
+namespace nerf {
+namespace {
+
+#define NERF_CUDA(expr)                                                                       \
+  do {                                                                                        \
+    cudaError_t _e = (expr);                                                                  \
+    if (_e != cudaSuccess) {                                                                  \
+      set_error(std::string(#expr) + ": " + cudaGetErrorString(_e));                          \
+      return NERF_E_CUDA;                                                                     \
+    }                                                                                         \
+  } while (0)
+
+// Grow-only device buffer.
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return NERF_OK;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    NERF_CUDA(cudaMalloc(&p, bytes));
+    cap = bytes;
+    return NERF_OK;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <class T>
+  T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct DeviceNet {
+  float* blob = nullptr;  // every f32 tensor of the network, file layout, 16-byte aligned segments
+  NetF32 f32{};
+  TcWeights tc[2];        // [0] bf16, [1] fp16 pre-swizzled operand tiles (mlp_tc.cu)
+};
+
+enum StageKind { ST_SAMPLING = 0, ST_MLP_COARSE, ST_MLP_FINE, ST_COMPOSITE, ST_COUNT };
+
+}  // namespace
+}  // namespace nerf
+
+using namespace nerf;
+
+struct nerf_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;  // used by the host entry points
+  std::recursive_mutex mu;
+  DeviceNet nets[2];
+  DevBuf dirs, tc, sigc, wc, tf, sigf, rgbf, out, in_a, in_b, jit, uni;
+  // timing
+  struct Span { cudaEvent_t a, b; int kind; };
+  std::vector<Span> spans;
+  size_t spans_used = 0;
+  cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+  bool have_timing = false;
+  int launches = 0;
+  int64_t chunk_rays = 1 << 20;
+};
+
+namespace nerf {
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    cudaGetDevice(&cur);
+    if (prev >= 0 && cur != prev) cudaSetDevice(prev);
+  }
+};
+
+int upload_network(const TensorMap& t, DeviceNet* net) {
+  static const char* const names[12] = {"dense0", "dense1", "dense2", "dense3", "dense4", "dense5",
+                                        "dense6", "dense7", "bottleneck", "viewdirs", "rgb", "alpha"};
+  size_t total = 0;
+  auto pad4 = [](size_t n) { return (n + 3) & ~(size_t)3; };
+  for (const char* n : names) {
+    total += pad4(t.at(std::string(n) + "_kernel").data.size());
+    total += pad4(t.at(std::string(n) + "_bias").data.size());
+  }
+  std::vector<float> host(total, 0.0f);
+  const float* dptr[24];
+  NERF_CUDA(cudaMalloc(&net->blob, total * sizeof(float)));
+  size_t off = 0;
+  for (int i = 0; i < 12; ++i) {
+    const auto& k = t.at(std::string(names[i]) + "_kernel").data;
+    const auto& b = t.at(std::string(names[i]) + "_bias").data;
+    std::memcpy(host.data() + off, k.data(), k.size() * 4);
+    dptr[2 * i] = net->blob + off;
+    off += pad4(k.size());
+    std::memcpy(host.data() + off, b.data(), b.size() * 4);
+    dptr[2 * i + 1] = net->blob + off;
+    off += pad4(b.size());
+  }
+  NERF_CUDA(cudaMemcpy(net->blob, host.data(), total * sizeof(float), cudaMemcpyHostToDevice));
+  for (int i = 0; i < 8; ++i) {
+    net->f32.w[i] = dptr[2 * i];
+    net->f32.b[i] = dptr[2 * i + 1];
+  }
+  net->f32.w_bott = dptr[16];  net->f32.b_bott = dptr[17];
+  net->f32.w_view = dptr[18];  net->f32.b_view = dptr[19];
+  net->f32.w_rgb = dptr[20];   net->f32.b_rgb = dptr[21];
+  net->f32.w_alpha = dptr[22]; net->f32.b_alpha = dptr[23];
+  // Pre-swizzled 16-bit operand tiles for the tensor-core kernel, one set per operand format.
+  for (int fmt = 0; fmt < 2; ++fmt) {
+    int rc = build_tc_weights(t, fmt, net->f32, &net->tc[fmt]);
+    if (rc != NERF_OK) return rc;
+  }
+  return NERF_OK;
+}
+
+int create_common(const TensorMap& coarse, const TensorMap& fine, int device, nerf_ctx** out) {
+  int rc = validate_network(coarse, "coarse");
+  if (rc != NERF_OK) return rc;
+  rc = validate_network(fine, "fine");
+  if (rc != NERF_OK) return rc;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+    set_error("no CUDA device: libnerf_b200 has no CPU fallback");
+    return NERF_E_CUDA;
+  }
+  if (device < 0 || device >= count) {
+    set_error("device ordinal out of range");
+    return NERF_E_ARG;
+  }
+  cudaDeviceProp prop;
+  NERF_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    set_error(std::string("device is sm_") + std::to_string(prop.major * 10 + prop.minor) +
+              "; libnerf_b200 is built for sm_100a only");
+    return NERF_E_CUDA;
+  }
+  DeviceGuard g(device);
+  nerf_ctx* ctx = new (std::nothrow) nerf_ctx();
+  if (!ctx) {
+    set_error("out of host memory");
+    return NERF_E_ARG;
+  }
+  ctx->device = device;
+  ctx->sm_count = prop.multiProcessorCount;
+  if (const char* e = std::getenv("NERF_B200_CHUNK_RAYS")) {
+    const long long v = std::atoll(e);
+    if (v > 0) ctx->chunk_rays = v;
+  }
+  cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev_begin);
+  if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev_end);
+  if (e != cudaSuccess) {
+    set_error(std::string("stream/event create: ") + cudaGetErrorString(e));
+    delete ctx;
+    return NERF_E_CUDA;
+  }
+  rc = upload_network(coarse, &ctx->nets[0]);
+  if (rc == NERF_OK) rc = upload_network(fine, &ctx->nets[1]);
+  if (rc != NERF_OK) {
+    nerf_destroy(ctx);
+    return rc;
+  }
+  *out = ctx;
+  return NERF_OK;
+}
+
+// get_ray_dir's pixel-independent part (src/lib.rs:216-226), evaluated once on the host.
+RayBasis make_basis(const nerf_camera& cam, int W, int H) {
+  RayBasis rb{};
+  normalize3(cam.forward, rb.f);  // f = dir.normalize()
+  float tmp[3];
+  cross3(rb.f, cam.up, tmp);
+  normalize3(tmp, rb.r);  // r = f x up, normalised
+  cross3(rb.r, rb.f, tmp);
+  normalize3(tmp, rb.u);  // u = r x f, normalised
+  rb.sx = std::tan(cam.alpha_w);
+  rb.sy = std::tan(cam.alpha_h);
+  for (int i = 0; i < 3; ++i) rb.origin[i] = cam.origin[i];
+  rb.near_ = cam.near_;
+  rb.far_ = cam.far_;
+  rb.nx = W;
+  rb.ny = H;
+  return rb;
+}
+
+void span_begin(nerf_ctx* c, int kind, cudaStream_t s) {
+  if (c->spans_used == c->spans.size()) {
+    nerf_ctx::Span sp{};
+    cudaEventCreate(&sp.a);
+    cudaEventCreate(&sp.b);
+    c->spans.push_back(sp);
+  }
+  c->spans[c->spans_used].kind = kind;
+  cudaEventRecord(c->spans[c->spans_used].a, s);
+}
+void span_end(nerf_ctx* c, cudaStream_t s) {
+  cudaEventRecord(c->spans[c->spans_used].b, s);
+  ++c->spans_used;
+}
+
+int run_mlp(nerf_ctx* c, int net, const SampleSrc& src, const SampleDst& dst, int precision, cudaStream_t s) {
+  if (src.B == 0) return NERF_OK;
+  cudaError_t e;
+  switch (precision) {
+    case NERF_PREC_FP32:
+      e = launch_mlp_fp32(c->nets[net].f32, src, dst, s);
+      break;
+    case NERF_PREC_BF16:
+      e = launch_mlp_tc(c->nets[net].tc[0], src, dst, c->sm_count, s);
+      break;
+    case NERF_PREC_FP16:
+    case NERF_PREC_TF32:
+      e = launch_mlp_tc(c->nets[net].tc[1], src, dst, c->sm_count, s);
+      break;
+    default:
+      set_error("unknown precision");
+      return NERF_E_ARG;
+  }
+  ++c->launches;
+  if (e != cudaSuccess) {
+    set_error(std::string("mlp launch: ") + cudaGetErrorString(e));
+    return NERF_E_CUDA;
+  }
+  return NERF_OK;
+}
+
+int check_render_args(const nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc, int nf, const nerf_sampling* smp,
+                      int64_t rb, int64_t re) {
+  if (!c || !cam) { set_error("null context or camera"); return NERF_E_ARG; }
+  if (nc <= 0) { set_error("coarse samples per ray must be greater than 0"); return NERF_E_ARG; }       // lib.rs:483-486
+  if (W <= 0 || W % 8 != 0) { set_error("image width must be multiple of block size"); return NERF_E_ARG; }   // lib.rs:492-496
+  if (H <= 0 || H % 8 != 0) { set_error("image height must be multiple of block size"); return NERF_E_ARG; }  // lib.rs:497-501
+  if (nf < 0) { set_error("negative fine sample count"); return NERF_E_ARG; }
+  if (nf > 0 && nc < 3) {
+    // sample_importance returns no samples for n < 3 (lib.rs:295-297), which makes rays ragged.
+    set_error("n_fine > 0 needs n_coarse >= 3 (ragged rays are not supported)");
+    return NERF_E_UNSUPPORTED;
+  }
+  if ((size_t)(6 * (size_t)nc + nf) * 8 * sizeof(float) > 200 * 1024) {
+    set_error("n_coarse/n_fine too large for the importance sampler's shared memory");
+    return NERF_E_UNSUPPORTED;
+  }
+  if (rb < 0 || re < rb || re > (int64_t)W * H) { set_error("bad ray range"); return NERF_E_ARG; }
+  if (smp && smp->mode == NERF_SAMPLING_ARRAYS && (!smp->jitter || (nf > 0 && !smp->u))) {
+    set_error("NERF_SAMPLING_ARRAYS needs jitter and u");
+    return NERF_E_ARG;
+  }
+  if (smp && (smp->mode < 0 || smp->mode > 2)) { set_error("unknown sampling mode"); return NERF_E_ARG; }
+  return NERF_OK;
+}
+
+struct StagePtrs {  // device destinations for stage dumps (may be null)
+  float *dirs = nullptr, *t_c = nullptr, *sigma_c = nullptr, *w_c = nullptr, *t_f = nullptr, *sigma_f = nullptr,
+        *rgb_f = nullptr;
+};
+
+// The kernel schedule of render_block (lib.rs:353-472) for rays [rb, re): K1 -> MLP(coarse) -> K3 ->
+// MLP(fine) -> K4.  d_jit/d_u are device pointers indexed from ray rb.
+int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int nf, int precision, int mode,
+                 uint64_t seed, const float* d_jit, const float* d_u, int64_t rb, int64_t re, float* d_rgb,
+                 bool want_wc, cudaStream_t s) {
+  const RayBasis basis = make_basis(cam, W, H);
+  const int nm = nc + nf;
+  for (int64_t b0 = rb; b0 < re; b0 += c->chunk_rays) {
+    const int64_t n = std::min<int64_t>(c->chunk_rays, re - b0);
+    const int64_t off = b0 - rb;
+    int rc;
+    if ((rc = c->dirs.reserve(n * 3 * 4)) || (rc = c->tc.reserve(n * nc * 4)) || (rc = c->sigc.reserve(n * nc * 4)) ||
+        (rc = c->tf.reserve(n * nm * 4)) || (rc = c->sigf.reserve(n * nm * 4)) || (rc = c->rgbf.reserve(n * nm * 12)) ||
+        (want_wc && (rc = c->wc.reserve(n * nc * 4))))
+      return rc;
+    span_begin(c, ST_SAMPLING, s);
+    NERF_CUDA(launch_raygen_stratified(basis, nc, mode, seed, d_jit ? d_jit + off * nc : nullptr, b0, n,
+                                       c->dirs.as<float>(), c->tc.as<float>(), s));
+    span_end(c, s);
+    ++c->launches;
+
+    SampleSrc src{};
+    src.mode = 1;
+    src.S = nc;
+    src.B = n * nc;
+    src.dirs = c->dirs.as<float>();
+    src.t = c->tc.as<float>();
+    for (int i = 0; i < 3; ++i) src.origin[i] = cam.origin[i];
+    SampleDst dst{c->sigc.as<float>(), nullptr};  // coarse colour is discarded by the reference (lib.rs:404)
+    span_begin(c, ST_MLP_COARSE, s);
+    rc = run_mlp(c, NERF_NET_COARSE, src, dst, precision, s);
+    span_end(c, s);
+    if (rc) return rc;
+
+    span_begin(c, ST_SAMPLING, s);
+    NERF_CUDA(launch_importance(c->tc.as<float>(), c->sigc.as<float>(), nullptr, nc, nf, cam.far_, mode, seed,
+                                d_u ? d_u + off * nf : nullptr, b0, n, c->tf.as<float>(),
+                                want_wc ? c->wc.as<float>() : nullptr, s));
+    span_end(c, s);
+    ++c->launches;
+
+    src.S = nm;
+    src.B = n * nm;
+    src.t = c->tf.as<float>();
+    dst = SampleDst{c->sigf.as<float>(), c->rgbf.as<float>()};
+    span_begin(c, ST_MLP_FINE, s);
+    rc = run_mlp(c, NERF_NET_FINE, src, dst, precision, s);
+    span_end(c, s);
+    if (rc) return rc;
+
+    span_begin(c, ST_COMPOSITE, s);
+    NERF_CUDA(launch_composite(c->rgbf.as<float>(), c->sigf.as<float>(), c->tf.as<float>(), n, nm, cam.far_,
+                               d_rgb + off * 3, s));
+    span_end(c, s);
+    ++c->launches;
+  }
+  return NERF_OK;
+}
+
+void timing_start(nerf_ctx* c, cudaStream_t s) {
+  c->spans_used = 0;
+  c->launches = 0;
+  c->have_timing = true;
+  cudaEventRecord(c->ev_begin, s);
+}
+void timing_stop(nerf_ctx* c, cudaStream_t s) { cudaEventRecord(c->ev_end, s); }
+
+}  // namespace
+}  // namespace nerf
+
+// ============================================================================ extern "C" entry points
+extern "C" {
+
+int nerf_create(const char* weights_root, int device, nerf_ctx** out) {
+  if (!weights_root || !out) {
+    set_error("nerf_create: null argument");
+    return NERF_E_ARG;
+  }
+  TensorMap coarse, fine;
+  int rc = load_tensor_dir(std::string(weights_root) + "/coarse", &coarse);  // lib.rs:651
+  if (rc != NERF_OK) return rc;
+  rc = load_tensor_dir(std::string(weights_root) + "/fine", &fine);  // lib.rs:652
+  if (rc != NERF_OK) return rc;
+  return create_common(coarse, fine, device, out);
+}
+
+int nerf_create_from_tensors(const nerf_tensor* coarse, int n_coarse, const nerf_tensor* fine, int n_fine, int device,
+                             nerf_ctx** out) {
+  if (!coarse || !fine || !out) {
+    set_error("nerf_create_from_tensors: null argument");
+    return NERF_E_ARG;
+  }
+  auto to_map = [](const nerf_tensor* ts, int n, TensorMap* m) -> int {
+    for (int i = 0; i < n; ++i) {
+      const nerf_tensor& t = ts[i];
+      if (!t.name || !t.data || t.ndim < 1 || t.ndim > 2) {
+        set_error("nerf_create_from_tensors: malformed tensor entry");
+        return NERF_E_SHAPE;
+      }
+      HostTensor h;
+      int64_t cnt = 1;
+      for (int d = 0; d < t.ndim; ++d) {
+        h.dims.push_back(t.dims[d]);
+        cnt *= t.dims[d];
+      }
+      h.data.assign(t.data, t.data + cnt);
+      (*m)[t.name] = std::move(h);
+    }
+    return NERF_OK;
+  };
+  TensorMap c, f;
+  int rc = to_map(coarse, n_coarse, &c);
+  if (rc != NERF_OK) return rc;
+  rc = to_map(fine, n_fine, &f);
+  if (rc != NERF_OK) return rc;
+  return create_common(c, f, device, out);
+}
+
+void nerf_destroy(nerf_ctx* c) {
+  if (!c) return;
+  {
+    DeviceGuard g(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    for (DevBuf* b : {&c->dirs, &c->tc, &c->sigc, &c->wc, &c->tf, &c->sigf, &c->rgbf, &c->out, &c->in_a, &c->in_b,
+                      &c->jit, &c->uni})
+      b->release();
+    for (auto& n : c->nets) {
+      if (n.blob) cudaFree(n.blob);
+      for (auto& t : n.tc) free_tc_weights(&t);
+    }
+    for (auto& sp : c->spans) {
+      cudaEventDestroy(sp.a);
+      cudaEventDestroy(sp.b);
+    }
+    if (c->ev_begin) cudaEventDestroy(c->ev_begin);
+    if (c->ev_end) cudaEventDestroy(c->ev_end);
+    if (c->stream) cudaStreamDestroy(c->stream);
+  }
+  delete c;
+}
+
+int nerf_forward_batch_device(nerf_ctx* c, int net, const float* d_points, const float* d_dirs, int64_t B,
+                              int precision, float* d_rgb, float* d_sigma, void* stream) {
+  if (!c || net < 0 || net > 1 || B < 0) {
+    set_error("nerf_forward_batch: bad argument");
+    return NERF_E_ARG;
+  }
+  if (B == 0) return NERF_OK;  // network.rs:199-201
+  if (!d_points || !d_dirs || !d_rgb || !d_sigma) {
+    set_error("nerf_forward_batch: null buffer");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  SampleSrc src{};
+  src.mode = 0;
+  src.B = B;
+  src.points = d_points;
+  src.dirs = d_dirs;
+  SampleDst dst{d_sigma, d_rgb};
+  timing_start(c, s);
+  span_begin(c, net == 0 ? ST_MLP_COARSE : ST_MLP_FINE, s);
+  int rc = run_mlp(c, net, src, dst, precision, s);
+  span_end(c, s);
+  timing_stop(c, s);
+  return rc;
+}
+
+int nerf_forward_batch(nerf_ctx* c, int net, const float* points, const float* dirs, int64_t B, int precision,
+                       float* rgb, float* sigma) {
+  if (!c || net < 0 || net > 1 || B < 0) {
+    set_error("nerf_forward_batch: bad argument");
+    return NERF_E_ARG;
+  }
+  if (B == 0) return NERF_OK;
+  if (!points || !dirs || !rgb || !sigma) {
+    set_error("nerf_forward_batch: null buffer");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  int rc;
+  if ((rc = c->in_a.reserve(B * 12)) || (rc = c->in_b.reserve(B * 12)) || (rc = c->rgbf.reserve(B * 12)) ||
+      (rc = c->sigf.reserve(B * 4)))
+    return rc;
+  NERF_CUDA(cudaMemcpyAsync(c->in_a.p, points, B * 12, cudaMemcpyHostToDevice, c->stream));
+  NERF_CUDA(cudaMemcpyAsync(c->in_b.p, dirs, B * 12, cudaMemcpyHostToDevice, c->stream));
+  rc = nerf_forward_batch_device(c, net, c->in_a.as<float>(), c->in_b.as<float>(), B, precision,
+                                 c->rgbf.as<float>(), c->sigf.as<float>(), c->stream);
+  if (rc != NERF_OK) return rc;
+  NERF_CUDA(cudaMemcpyAsync(rgb, c->rgbf.p, B * 12, cudaMemcpyDeviceToHost, c->stream));
+  NERF_CUDA(cudaMemcpyAsync(sigma, c->sigf.p, B * 4, cudaMemcpyDeviceToHost, c->stream));
+  NERF_CUDA(cudaStreamSynchronize(c->stream));
+  return NERF_OK;
+}
+
+int nerf_render_device(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc, int nf, int precision,
+                       const nerf_sampling* smp, int64_t rb, int64_t re, float* d_rgb, void* stream) {
+  int rc = check_render_args(c, cam, W, H, nc, nf, smp, rb, re);
+  if (rc != NERF_OK) return rc;
+  if (re == rb) return NERF_OK;
+  if (!d_rgb) {
+    set_error("nerf_render: null output");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int mode = smp ? smp->mode : NERF_SAMPLING_DET;
+  timing_start(c, s);
+  rc = render_range(c, *cam, W, H, nc, nf, precision, mode, smp ? smp->seed : 0, smp ? smp->jitter : nullptr,
+                    smp ? smp->u : nullptr, rb, re, d_rgb, false, s);
+  timing_stop(c, s);
+  return rc;
+}
+
+static int render_host(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc, int nf, int precision,
+                       const nerf_sampling* smp, int64_t rb, int64_t re, float* rgb, const nerf_stages* st) {
+  int rc = check_render_args(c, cam, W, H, nc, nf, smp, rb, re);
+  if (rc != NERF_OK) return rc;
+  const int64_t n = re - rb;
+  if (n == 0) return NERF_OK;
+  if (!rgb) {
+    set_error("nerf_render: null output");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  cudaStream_t s = c->stream;
+  const int mode = smp ? smp->mode : NERF_SAMPLING_DET;
+  const float *d_jit = nullptr, *d_u = nullptr;
+  if (mode == NERF_SAMPLING_ARRAYS) {
+    if ((rc = c->jit.reserve(n * nc * 4)) || (rc = c->uni.reserve(std::max<int64_t>(n * nf, 1) * 4))) return rc;
+    NERF_CUDA(cudaMemcpyAsync(c->jit.p, smp->jitter, n * nc * 4, cudaMemcpyHostToDevice, s));
+    if (nf > 0) NERF_CUDA(cudaMemcpyAsync(c->uni.p, smp->u, n * nf * 4, cudaMemcpyHostToDevice, s));
+    d_jit = c->jit.as<float>();
+    d_u = c->uni.as<float>();
+  }
+  if ((rc = c->out.reserve(n * 12))) return rc;
+  const bool want_stages = st != nullptr;
+  const int64_t saved_chunk = c->chunk_rays;
+  if (want_stages) c->chunk_rays = n;  // stage dumps read the workspaces of a single chunk
+  timing_start(c, s);
+  rc = render_range(c, *cam, W, H, nc, nf, precision, mode, smp ? smp->seed : 0, d_jit, d_u, rb, re,
+                    c->out.as<float>(), want_stages && st->w_c, s);
+  timing_stop(c, s);
+  c->chunk_rays = saved_chunk;
+  if (rc != NERF_OK) return rc;
+  NERF_CUDA(cudaMemcpyAsync(rgb, c->out.p, n * 12, cudaMemcpyDeviceToHost, s));
+  if (want_stages) {
+    const int nm = nc + nf;
+    auto d2h = [&](float* dst, const DevBuf& b, size_t bytes) -> cudaError_t {
+      return dst ? cudaMemcpyAsync(dst, b.p, bytes, cudaMemcpyDeviceToHost, s) : cudaSuccess;
+    };
+    NERF_CUDA(d2h(st->dirs, c->dirs, n * 12));
+    NERF_CUDA(d2h(st->t_c, c->tc, n * nc * 4));
+    NERF_CUDA(d2h(st->sigma_c, c->sigc, n * nc * 4));
+    NERF_CUDA(d2h(st->w_c, c->wc, n * nc * 4));
+    NERF_CUDA(d2h(st->t_f, c->tf, n * nm * 4));
+    NERF_CUDA(d2h(st->sigma_f, c->sigf, n * nm * 4));
+    NERF_CUDA(d2h(st->rgb_f, c->rgbf, n * nm * 12));
+  }
+  NERF_CUDA(cudaStreamSynchronize(s));
+  return NERF_OK;
+}
+
+int nerf_render(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc, int nf, int precision,
+                const nerf_sampling* smp, int64_t rb, int64_t re, float* rgb) {
+  return render_host(c, cam, W, H, nc, nf, precision, smp, rb, re, rgb, nullptr);
+}
+
+int nerf_render_stages(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc, int nf, int precision,
+                       const nerf_sampling* smp, int64_t rb, int64_t re, float* rgb, const nerf_stages* st) {
+  static const nerf_stages none{};
+  return render_host(c, cam, W, H, nc, nf, precision, smp, rb, re, rgb, st ? st : &none);
+}
+
+int nerf_ray_dirs(nerf_ctx* c, const nerf_camera* cam, int W, int H, int64_t rb, int64_t re, float* dirs) {
+  if (!c || !cam || W <= 0 || H <= 0 || rb < 0 || re < rb || re > (int64_t)W * H || (!dirs && re > rb)) {
+    set_error("nerf_ray_dirs: bad argument");
+    return NERF_E_ARG;
+  }
+  const int64_t n = re - rb;
+  if (n == 0) return NERF_OK;
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  int rc;
+  if ((rc = c->dirs.reserve(n * 12))) return rc;
+  NERF_CUDA(launch_ray_dirs(make_basis(*cam, W, H), rb, n, c->dirs.as<float>(), c->stream));
+  NERF_CUDA(cudaMemcpyAsync(dirs, c->dirs.p, n * 12, cudaMemcpyDeviceToHost, c->stream));
+  NERF_CUDA(cudaStreamSynchronize(c->stream));
+  return NERF_OK;
+}
+
+int nerf_compute_weights(nerf_ctx* c, const float* sigma, const float* t, int64_t n_rays, int n, float far_,
+                         float* w) {
+  if (!c || n_rays < 0 || n < 0 || ((!sigma || !t || !w) && n_rays * n > 0)) {
+    set_error("nerf_compute_weights: bad argument");
+    return NERF_E_ARG;
+  }
+  const int64_t cnt = n_rays * n;
+  if (cnt == 0) return NERF_OK;
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  int rc;
+  if ((rc = c->sigc.reserve(cnt * 4)) || (rc = c->tc.reserve(cnt * 4)) || (rc = c->wc.reserve(cnt * 4))) return rc;
+  NERF_CUDA(cudaMemcpyAsync(c->sigc.p, sigma, cnt * 4, cudaMemcpyHostToDevice, c->stream));
+  NERF_CUDA(cudaMemcpyAsync(c->tc.p, t, cnt * 4, cudaMemcpyHostToDevice, c->stream));
+  NERF_CUDA(launch_weights(c->sigc.as<float>(), c->tc.as<float>(), n_rays, n, far_, c->wc.as<float>(), c->stream));
+  NERF_CUDA(cudaMemcpyAsync(w, c->wc.p, cnt * 4, cudaMemcpyDeviceToHost, c->stream));
+  NERF_CUDA(cudaStreamSynchronize(c->stream));
+  return NERF_OK;
+}
+
+// sample_importance (lib.rs:289-351) on caller-supplied weights, followed by render_block's merge + sort
+// (lib.rs:416-420).
+int nerf_sample_importance(nerf_ctx* c, const float* t, const float* w, int64_t n_rays, int n, const float* u,
+                           int count, float* t_merged) {
+  if (!c || n_rays < 0 || n < 3 || count < 0 || ((!t || !w || !t_merged) && n_rays > 0) || (count > 0 && !u)) {
+    set_error("nerf_sample_importance: bad argument (n must be >= 3)");
+    return NERF_E_ARG;
+  }
+  if (n_rays == 0) return NERF_OK;
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  const int nm = n + count;
+  int rc;
+  if ((rc = c->wc.reserve(n_rays * n * 4)) || (rc = c->tc.reserve(n_rays * n * 4)) ||
+      (rc = c->uni.reserve(std::max<int64_t>(n_rays * count, 1) * 4)) || (rc = c->tf.reserve(n_rays * nm * 4)))
+    return rc;
+  NERF_CUDA(cudaMemcpyAsync(c->wc.p, w, n_rays * n * 4, cudaMemcpyHostToDevice, c->stream));
+  NERF_CUDA(cudaMemcpyAsync(c->tc.p, t, n_rays * n * 4, cudaMemcpyHostToDevice, c->stream));
+  if (count > 0) NERF_CUDA(cudaMemcpyAsync(c->uni.p, u, n_rays * count * 4, cudaMemcpyHostToDevice, c->stream));
+  NERF_CUDA(launch_importance(c->tc.as<float>(), nullptr, c->wc.as<float>(), n, count, 0.0f, NERF_SAMPLING_ARRAYS, 0,
+                              c->uni.as<float>(), 0, n_rays, c->tf.as<float>(), nullptr, c->stream));
+  NERF_CUDA(cudaMemcpyAsync(t_merged, c->tf.p, n_rays * nm * 4, cudaMemcpyDeviceToHost, c->stream));
+  NERF_CUDA(cudaStreamSynchronize(c->stream));
+  return NERF_OK;
+}
+
+int nerf_integrate_rays(nerf_ctx* c, const float* rgb, const float* sigma, const float* t, int64_t n_rays, int n,
+                        float far_, float* out) {
+  if (!c || n_rays < 0 || n < 0 || ((!rgb || !sigma || !t) && n_rays * n > 0) || (!out && n_rays > 0)) {
+    set_error("nerf_integrate_rays: bad argument");
+    return NERF_E_ARG;
+  }
+  if (n_rays == 0) return NERF_OK;
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  const int64_t cnt = std::max<int64_t>(n_rays * n, 1);
+  int rc;
+  if ((rc = c->rgbf.reserve(cnt * 12)) || (rc = c->sigf.reserve(cnt * 4)) || (rc = c->tf.reserve(cnt * 4)) ||
+      (rc = c->out.reserve(n_rays * 12)))
+    return rc;
+  if (n > 0) {
+    NERF_CUDA(cudaMemcpyAsync(c->rgbf.p, rgb, n_rays * n * 12, cudaMemcpyHostToDevice, c->stream));
+    NERF_CUDA(cudaMemcpyAsync(c->sigf.p, sigma, n_rays * n * 4, cudaMemcpyHostToDevice, c->stream));
+    NERF_CUDA(cudaMemcpyAsync(c->tf.p, t, n_rays * n * 4, cudaMemcpyHostToDevice, c->stream));
+  }
+  NERF_CUDA(launch_composite(c->rgbf.as<float>(), c->sigf.as<float>(), c->tf.as<float>(), n_rays, n, far_,
+                             c->out.as<float>(), c->stream));
+  NERF_CUDA(cudaMemcpyAsync(out, c->out.p, n_rays * 12, cudaMemcpyDeviceToHost, c->stream));
+  NERF_CUDA(cudaStreamSynchronize(c->stream));
+  return NERF_OK;
+}
+
+int nerf_get_timing(nerf_ctx* c, nerf_timing* out) {
+  if (!c || !out) {
+    set_error("nerf_get_timing: null argument");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  std::memset(out, 0, sizeof(*out));
+  if (!c->have_timing) return NERF_OK;
+  NERF_CUDA(cudaEventSynchronize(c->ev_end));
+  NERF_CUDA(cudaEventElapsedTime(&out->total_ms, c->ev_begin, c->ev_end));
+  for (size_t i = 0; i < c->spans_used; ++i) {
+    float ms = 0.0f;
+    NERF_CUDA(cudaEventElapsedTime(&ms, c->spans[i].a, c->spans[i].b));
+    switch (c->spans[i].kind) {
+      case ST_SAMPLING: out->sampling_ms += ms; break;
+      case ST_MLP_COARSE: out->mlp_coarse_ms += ms; break;
+      case ST_MLP_FINE: out->mlp_fine_ms += ms; break;
+      case ST_COMPOSITE: out->composite_ms += ms; break;
+    }
+  }
+  out->kernel_launches = c->launches;
+  return NERF_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,103 @@
+// common.cuh — shared device/host declarations of libnerf_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/nerf_b200.h"
+
+namespace nerf {
+
+// ------------------------------------------------------------------ network dimensions (shapes.txt)
+constexpr int kPosOctaves = 10;          // network.rs:204
+constexpr int kDirOctaves = 4;           // network.rs:219
+constexpr int kPosEnc = 3 + 6 * kPosOctaves;  // 63
+constexpr int kDirEnc = 3 + 6 * kDirOctaves;  // 27
+constexpr int kHidden = 256;
+constexpr int kViewHidden = 128;
+constexpr int kSkipIn = kPosEnc + kHidden;    // 319, [h0; h4] (network.rs:210)
+constexpr int kViewIn = kHidden + kDirEnc;    // 283, [bottleneck; PE4(dir)] (network.rs:220)
+
+// f32 weights of one network on the device, in the file layout ([in][out] row-major).
+struct NetF32 {
+  const float* w[8];   // dense0..7
+  const float* b[8];
+  const float* w_bott; // [256][256]
+  const float* b_bott;
+  const float* w_view; // [283][128]
+  const float* b_view;
+  const float* w_rgb;  // [128][3]
+  const float* b_rgb;
+  const float* w_alpha;  // [256][1]
+  const float* b_alpha;
+};
+
+// Where the samples of an MLP launch come from.
+//   mode 0: forward_batch — points [3][B] feature-major + dirs [B][3]          (network.rs:197)
+//   mode 1: render        — sample g belongs to ray g / S; p = origin + dir_hat * t   (lib.rs:396,436)
+struct SampleSrc {
+  int mode;
+  int S;                // samples per ray (mode 1)
+  int64_t B;            // number of samples
+  const float* points;  // mode 0
+  const float* dirs;    // mode 0: [B][3]; mode 1: [n_rays][3]
+  const float* t;       // mode 1: [n_rays][S]
+  float origin[3];
+};
+
+struct SampleDst {
+  float* sigma;  // [B]
+  float* rgb;    // [B][3] or nullptr: skip bottleneck/viewdirs/rgb (the reference discards coarse rgb, lib.rs:404)
+};
+
+// Camera constants hoisted out of get_ray_dir (lib.rs:216-226): they do not depend on the pixel, so
+// evaluating them once on the host (glibc tanf, IEEE sqrt/div) is bit-identical to the reference.
+struct RayBasis {
+  float f[3], r[3], u[3];
+  float sx, sy;
+  float origin[3];
+  float near_, far_;
+  int nx, ny;
+};
+
+// ------------------------------------------------------------------ Philox4x32-10 (shared with oracle)
+__host__ __device__ inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint64_t p0 = (uint64_t)0xD2511F53u * c[0];
+    uint64_t p1 = (uint64_t)0xCD9E8D57u * c[2];
+    uint32_t n0 = (uint32_t)(p1 >> 32) ^ c[1] ^ k0;
+    uint32_t n1 = (uint32_t)p1;
+    uint32_t n2 = (uint32_t)(p0 >> 32) ^ c[3] ^ k1;
+    uint32_t n3 = (uint32_t)p0;
+    c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+}
+// k-th uniform of (seed, pixel, stream): block k/4, element k%4, float = (x >> 8) * 2^-24 in [0,1).
+__host__ __device__ inline float philox_uniform(uint64_t seed, uint32_t pixel, uint32_t stream, int k) {
+  uint32_t c[4] = {pixel, (uint32_t)(k >> 2), stream, 0u};
+  philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+  return (float)(c[k & 3] >> 8) * (1.0f / 16777216.0f);
+}
+
+// ------------------------------------------------------------------ kernel launchers (one per .cu)
+// mlp_fp32.cu
+cudaError_t launch_mlp_fp32(const NetF32& net, const SampleSrc& src, const SampleDst& dst, cudaStream_t s);
+// sampling.cu
+cudaError_t launch_raygen_stratified(const RayBasis& rb, int nc, int mode, uint64_t seed, const float* d_jitter,
+                                     int64_t ray_begin, int64_t n_rays, float* d_dirs, float* d_tc, cudaStream_t s);
+cudaError_t launch_ray_dirs(const RayBasis& rb, int64_t ray_begin, int64_t n_rays, float* d_dirs, cudaStream_t s);
+// weights come from d_sigc (compute_weights) unless d_w_in is given (stage entry point).
+cudaError_t launch_importance(const float* d_tc, const float* d_sigc, const float* d_w_in, int nc, int nf, float far_,
+                              int mode,
+                              uint64_t seed, const float* d_u, int64_t ray_begin, int64_t n_rays, float* d_tf,
+                              float* d_wc_or_null, cudaStream_t s);
+cudaError_t launch_weights(const float* d_sigma, const float* d_t, int64_t n_rays, int n, float far_, float* d_w,
+                           cudaStream_t s);
+cudaError_t launch_composite(const float* d_rgb, const float* d_sigma, const float* d_t, int64_t n_rays, int n,
+                             float far_, float* d_out, cudaStream_t s);
+
+}  // namespace nerf

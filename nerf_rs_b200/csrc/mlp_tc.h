@@ -1,0 +1,33 @@
+// mlp_tc.h — the fused tcgen05/TMEM MLP kernel (mlp_tc.cu): weight tiles, constants and launcher.
+#pragma once
+#include "common.cuh"
+#include "host_util.h"
+
+namespace nerf {
+
+// Small f32 tables the epilogue needs; passed to the kernel as a __grid_constant__ parameter so they
+// are served from the constant bank.
+struct TcConsts {
+  float bias[10][256];   // dense0..7, bottleneck, viewdirs (128 used)
+  float w_alpha[256];    // sigma head weights (network.rs:216), evaluated in f32 in the epilogue
+  float w_rgb[128 * 3];  // rgb head weights [128][3] (network.rs:223)
+  float b_rgb[3];
+  float b_alpha;
+};
+
+// Pre-swizzled 16-bit operand tiles of one network (one operand format), in consumption order.
+// Each chunk is the exact shared-memory image of a [N x 64] K-major SWIZZLE_128B tcgen05 B operand
+// (N=256: 32 KiB; viewdirs N=128: 16 KiB), so the kernel streams it with a 1-D bulk TMA copy.
+struct TcWeights {
+  uint8_t* d_chunks = nullptr;
+  size_t bytes = 0;
+  int fmt = 0;  // 0 = bf16, 1 = fp16
+  TcConsts consts;
+};
+
+int build_tc_weights(const TensorMap& t, int fmt, const NetF32& f32, TcWeights* out);
+void free_tc_weights(TcWeights* w);
+cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
+                          cudaStream_t s);
+
+}  // namespace nerf

@@ -1,0 +1,304 @@
+// sampling.cu — ray generation, stratified sampling, hierarchical importance resampling and alpha
+// compositing as sm_100a kernels.  These are HBM-bound stages (K1 268 B/ray, K3 1 280 B/ray,
+// K4 3 856 B/ray); one warp owns one ray, loads are lane-strided (coalesced), transmittance is a warp-level
+// exclusive product scan.  Compiled with -fmad=false: every mul/add rounds separately, as in the
+// reference's f32 Rust arithmetic (rustc never contracts).
+//
+// Reference functions restated here (file:line into elisabeth96/nerf-rs):
+//   get_ray_dir + normalize   src/lib.rs:214-230, :371      stratified_samples  src/lib.rs:233-248
+//   compute_weights           src/lib.rs:250-283            midpoints           src/lib.rs:285-287
+//   sample_importance         src/lib.rs:289-351            merge + sort        src/lib.rs:416-420
+//   integrate_ray             src/lib.rs:176-195
+#include "common.cuh"
+
+namespace nerf {
+
+namespace {
+
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kWarpsPerCta = 8;
+
+__device__ __forceinline__ void ray_dir_normalized(const RayBasis& rb, int64_t pixel, float out[3]) {
+  const int i = (int)(pixel / rb.nx), j = (int)(pixel % rb.nx);  // pixel_index = i*nx + j (lib.rs:371)
+  const float x = (((float)j + 0.5f) / (float)rb.nx) * 2.0f - 1.0f;  // lib.rs:221
+  const float y = 1.0f - (((float)i + 0.5f) / (float)rb.ny) * 2.0f;  // lib.rs:222
+  const float a = x * rb.sx, b = y * rb.sy;
+  const float dx = (rb.r[0] * a + rb.u[0] * b) + rb.f[0];  // r*(x*sx) + u*(y*sy) + f (lib.rs:229)
+  const float dy = (rb.r[1] * a + rb.u[1] * b) + rb.f[1];
+  const float dz = (rb.r[2] * a + rb.u[2] * b) + rb.f[2];
+  const float len = sqrtf(dx * dx + dy * dy + dz * dz);  // vec3.rs:27-34: three divisions, not an rsqrt
+  out[0] = dx / len;
+  out[1] = dy / len;
+  out[2] = dz / len;
+}
+
+// K1: one thread per (ray, coarse sample); thread s==0 of a ray also writes the direction.
+__global__ void __launch_bounds__(256) raygen_stratified_kernel(RayBasis rb, int nc, int mode, uint64_t seed,
+                                                               const float* __restrict__ jitter,
+                                                               int64_t ray_begin, int64_t n_rays,
+                                                               float* __restrict__ dirs, float* __restrict__ tc) {
+  const int64_t total = n_rays * nc;
+  const float interval = (rb.far_ - rb.near_) / (float)nc;  // lib.rs:239
+  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t ray = e / nc;
+    const int s = (int)(e - ray * nc);
+    const int64_t pixel = ray_begin + ray;
+    float jit;
+    if (mode == NERF_SAMPLING_DET) jit = 0.5f;
+    else if (mode == NERF_SAMPLING_PHILOX) jit = philox_uniform(seed, (uint32_t)pixel, 0u, s);
+    else jit = jitter[e];
+    const float lower = rb.near_ + (float)s * interval;  // lib.rs:241
+    const float upper = lower + interval;                // lib.rs:242
+    tc[e] = lower + (upper - lower) * jit;               // lib.rs:244
+    if (s == 0) {
+      float d[3];
+      ray_dir_normalized(rb, pixel, d);
+      dirs[ray * 3 + 0] = d[0];
+      dirs[ray * 3 + 1] = d[1];
+      dirs[ray * 3 + 2] = d[2];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) ray_dirs_kernel(RayBasis rb, int64_t ray_begin, int64_t n_rays,
+                                                      float* __restrict__ dirs) {
+  for (int64_t ray = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; ray < n_rays;
+       ray += (int64_t)gridDim.x * blockDim.x) {
+    float d[3];
+    ray_dir_normalized(rb, ray_begin + ray, d);
+    dirs[ray * 3 + 0] = d[0];
+    dirs[ray * 3 + 1] = d[1];
+    dirs[ray * 3 + 2] = d[2];
+  }
+}
+
+// compute_weights (lib.rs:250-283) for 32 consecutive samples [base, base+32) of one ray, one per lane.
+// `carry` is the transmittance before sample `base`; returns this lane's weight and updates carry.
+// T before sample i is an exclusive product scan of (1 - alpha).  The reference zeroes every weight after
+// the first sample whose running T drops below 1e-4; T is non-increasing, so that is exactly "T before
+// sample i < 1e-4".
+__device__ __forceinline__ float warp_weights_round(const float* sig, const float* t, int n, float far_, int base,
+                                                    int lane, float& carry) {
+  const int i = base + lane;
+  float alpha = 0.0f;
+  if (i < n) {
+    float delta = (i + 1 < n) ? (t[i + 1] - t[i]) : (far_ - t[i]);  // lib.rs:262-266
+    if (delta < 0.0f) delta = 0.0f;                                  // lib.rs:267-269
+    alpha = 1.0f - expf(-sig[i] * delta);                            // lib.rs:271
+  }
+  float p = 1.0f - alpha;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const float q = __shfl_up_sync(kFull, p, d);
+    if (lane >= d) p *= q;
+  }
+  float excl = __shfl_up_sync(kFull, p, 1);
+  if (lane == 0) excl = 1.0f;
+  const float t_before = carry * excl;
+  carry = carry * __shfl_sync(kFull, p, 31);
+  return (t_before < 1e-4f) ? 0.0f : t_before * alpha;  // lib.rs:272-279
+}
+
+// K3: coarse weights -> pdf -> cdf -> inverse-CDF samples -> merge with coarse t -> stable sort.
+// Per-warp shared memory: t[nc] w[nc] pdf[nc] cdf[nc] bins[nc] merged[nc+nf].
+__global__ void __launch_bounds__(kWarpsPerCta * 32) importance_kernel(
+    const float* __restrict__ tc, const float* __restrict__ sigc, const float* __restrict__ w_in, int nc, int nf,
+    float far_, int mode, uint64_t seed,
+    const float* __restrict__ u_in, int64_t ray_begin, int64_t n_rays, float* __restrict__ tf,
+    float* __restrict__ wc_out) {
+  extern __shared__ float smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nm = nc + nf;
+  float* s_t = smem + (size_t)warp * (5 * nc + nm);
+  float* s_w = s_t + nc;
+  float* s_pdf = s_w + nc;
+  float* s_cdf = s_pdf + nc;
+  float* s_bins = s_cdf + nc;
+  float* s_m = s_bins + nc;
+  const int m = nc - 2;  // pdf_weights = weights[1..n-1] (lib.rs:299)
+
+  for (int64_t ray = blockIdx.x * (int64_t)kWarpsPerCta + warp; ray < n_rays; ray += (int64_t)gridDim.x * kWarpsPerCta) {
+    const float* tr = tc + ray * nc;
+    const float* sr = sigc + ray * nc;
+    for (int i = lane; i < nc; i += 32) {
+      const float tv = tr[i];
+      s_t[i] = tv;
+      s_m[i] = tv;  // merged = coarse_ts.clone() (lib.rs:416)
+    }
+    __syncwarp();
+    if (w_in != nullptr) {
+      for (int i = lane; i < nc; i += 32) s_w[i] = w_in[ray * nc + i];
+    } else {
+      float carry = 1.0f;
+      for (int base = 0; base < nc; base += 32) {
+        const float w = warp_weights_round(sr, s_t, nc, far_, base, lane, carry);
+        if (base + lane < nc) {
+          s_w[base + lane] = w;
+          if (wc_out) wc_out[ray * nc + base + lane] = w;
+        }
+      }
+    }
+    __syncwarp();
+    if (nf > 0) {
+      for (int i = lane; i < m; i += 32) s_pdf[i] = fmaxf(s_w[i + 1], 0.0f) + 1e-5f;  // lib.rs:309
+      for (int i = lane; i < nc - 1; i += 32) s_bins[i] = 0.5f * (s_t[i] + s_t[i + 1]);  // lib.rs:286
+      __syncwarp();
+      float sum = 0.0f;
+      if (lane == 0)
+        for (int i = 0; i < m; ++i) sum += s_pdf[i];  // sequential fold, as iter().sum() (lib.rs:310)
+      sum = __shfl_sync(kFull, sum, 0);
+      for (int i = lane; i < m; i += 32) s_pdf[i] = s_pdf[i] / sum;  // lib.rs:315-317
+      __syncwarp();
+      if (lane == 0) {  // sequential prefix sum keeps the reference's rounding of every bin edge (lib.rs:319-328)
+        float cum = 0.0f;
+        s_cdf[0] = 0.0f;
+        for (int i = 0; i < m; ++i) {
+          cum += s_pdf[i];
+          s_cdf[i + 1] = cum;
+        }
+        s_cdf[m] = 1.0f;
+      }
+      __syncwarp();
+      const int64_t pixel = ray_begin + ray;
+      for (int k = lane; k < nf; k += 32) {
+        float uu;
+        if (mode == NERF_SAMPLING_DET) uu = ((float)k + 0.5f) / (float)nf;
+        else if (mode == NERF_SAMPLING_PHILOX) uu = philox_uniform(seed, (uint32_t)pixel, 1u, k);
+        else uu = u_in[ray * nf + k];
+        int idx = m - 1;  // lib.rs:333
+        for (int j = 0; j < m; ++j) {
+          if (uu >= s_cdf[j] && uu < s_cdf[j + 1]) {  // first match (lib.rs:334-339)
+            idx = j;
+            break;
+          }
+        }
+        const float lo = s_cdf[idx], hi = s_cdf[idx + 1];
+        const float denom = fmaxf(hi - lo, 1e-6f);  // lib.rs:343
+        const float bl = s_bins[idx], bu = s_bins[idx + 1];
+        const float tt = (uu - lo) / denom;
+        s_m[nc + k] = bl + (bu - bl) * tt;  // lib.rs:347
+      }
+      __syncwarp();
+    }
+    // Stable sort of merged[nm] (sort_by partial_cmp, lib.rs:419) by ranking: every element counts the
+    // elements that precede it.  All lanes read the same s_m[j] (broadcast), no bank conflicts.
+    float* out = tf + ray * nm;
+    for (int e = lane; e < nm; e += 32) {
+      const float v = s_m[e];
+      int rank = 0;
+      for (int j = 0; j < nm; ++j) {
+        const float o = s_m[j];
+        rank += (o < v || (o == v && j < e)) ? 1 : 0;
+      }
+      out[rank] = v;
+    }
+    __syncwarp();
+  }
+}
+
+// compute_weights alone (stage parity entry point).
+__global__ void __launch_bounds__(kWarpsPerCta * 32) weights_kernel(const float* __restrict__ sigma,
+                                                                    const float* __restrict__ t, int64_t n_rays,
+                                                                    int n, float far_, float* __restrict__ w) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int64_t ray = blockIdx.x * (int64_t)kWarpsPerCta + warp; ray < n_rays; ray += (int64_t)gridDim.x * kWarpsPerCta) {
+    float carry = 1.0f;
+    for (int base = 0; base < n; base += 32) {
+      const float wi = warp_weights_round(sigma + ray * n, t + ray * n, n, far_, base, lane, carry);
+      if (base + lane < n) w[ray * n + base + lane] = wi;
+    }
+  }
+}
+
+// K4: integrate_ray (lib.rs:176-195): rgb = sum w_i c_i + (1 - sum w_i) * white.
+__global__ void __launch_bounds__(kWarpsPerCta * 32) composite_kernel(const float* __restrict__ rgb,
+                                                                      const float* __restrict__ sigma,
+                                                                      const float* __restrict__ t, int64_t n_rays,
+                                                                      int n, float far_, float* __restrict__ out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int64_t ray = blockIdx.x * (int64_t)kWarpsPerCta + warp; ray < n_rays; ray += (int64_t)gridDim.x * kWarpsPerCta) {
+    const float* sr = sigma + ray * n;
+    const float* tr = t + ray * n;
+    const float* cr = rgb + ray * n * 3;
+    float r = 0.0f, g = 0.0f, b = 0.0f, acc = 0.0f, carry = 1.0f;
+    for (int base = 0; base < n; base += 32) {
+      const int i = base + lane;
+      float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f;
+      if (i < n) {
+        c0 = cr[i * 3 + 0];
+        c1 = cr[i * 3 + 1];
+        c2 = cr[i * 3 + 2];
+      }
+      const float wi = warp_weights_round(sr, tr, n, far_, base, lane, carry);
+      r += c0 * wi;
+      g += c1 * wi;
+      b += c2 * wi;
+      acc += wi;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      r += __shfl_xor_sync(kFull, r, d);
+      g += __shfl_xor_sync(kFull, g, d);
+      b += __shfl_xor_sync(kFull, b, d);
+      acc += __shfl_xor_sync(kFull, acc, d);
+    }
+    if (n == 0) { r = g = b = 0.0f; acc = 1.0f; }  // lib.rs:178-180: no samples -> black
+    const float bg = 1.0f - acc;                   // lib.rs:194
+    const float v = lane == 0 ? r + bg : (lane == 1 ? g + bg : b + bg);
+    if (lane < 3) out[ray * 3 + lane] = v;  // one 12-byte coalesced store per ray
+  }
+}
+
+inline int grid_for(int64_t work_items, int per_cta) {
+  int64_t g = (work_items + per_cta - 1) / per_cta;
+  const int64_t cap = 148 * 16;  // 16 resident CTAs of 256 threads would oversubscribe; loops stride the rest
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+}  // namespace
+
+cudaError_t launch_raygen_stratified(const RayBasis& rb, int nc, int mode, uint64_t seed, const float* d_jitter,
+                                     int64_t ray_begin, int64_t n_rays, float* d_dirs, float* d_tc, cudaStream_t s) {
+  if (n_rays == 0) return cudaSuccess;
+  raygen_stratified_kernel<<<grid_for(n_rays * nc, 256), 256, 0, s>>>(rb, nc, mode, seed, d_jitter, ray_begin, n_rays,
+                                                                       d_dirs, d_tc);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_ray_dirs(const RayBasis& rb, int64_t ray_begin, int64_t n_rays, float* d_dirs, cudaStream_t s) {
+  if (n_rays == 0) return cudaSuccess;
+  ray_dirs_kernel<<<grid_for(n_rays, 256), 256, 0, s>>>(rb, ray_begin, n_rays, d_dirs);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_importance(const float* d_tc, const float* d_sigc, const float* d_w_in, int nc, int nf, float far_,
+                              int mode, uint64_t seed, const float* d_u, int64_t ray_begin, int64_t n_rays, float* d_tf,
+                              float* d_wc, cudaStream_t s) {
+  if (n_rays == 0) return cudaSuccess;
+  const size_t smem = (size_t)kWarpsPerCta * (5 * (size_t)nc + nc + nf) * sizeof(float);
+  if (smem > 200 * 1024) return cudaErrorInvalidValue;
+  cudaError_t e = cudaFuncSetAttribute(importance_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  importance_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, smem, s>>>(
+      d_tc, d_sigc, d_w_in, nc, nf, far_, mode, seed, d_u, ray_begin, n_rays, d_tf, d_wc);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_weights(const float* d_sigma, const float* d_t, int64_t n_rays, int n, float far_, float* d_w,
+                           cudaStream_t s) {
+  if (n_rays == 0 || n == 0) return cudaSuccess;
+  weights_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, 0, s>>>(d_sigma, d_t, n_rays, n, far_, d_w);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_composite(const float* d_rgb, const float* d_sigma, const float* d_t, int64_t n_rays, int n,
+                             float far_, float* d_out, cudaStream_t s) {
+  if (n_rays == 0) return cudaSuccess;
+  composite_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, 0, s>>>(d_rgb, d_sigma, d_t, n_rays, n, far_,
+                                                                                d_out);
+  return cudaGetLastError();
+}
+
+}  // namespace nerf

@@ -1,0 +1,193 @@
+"""CPU suite: pins the oracle against the reference's only golden (tf_reference_samples.json, mirrored by the
+reference's own unit test src/lib.rs:753-916) and checks the host-side boundary logic.  No GPU needed."""
+import ctypes as C
+import os
+import struct
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle as O
+
+from .conftest import CAM_JSON, DATA
+
+
+def _example_inputs(golden, ex):
+    """The reference test's inputs (lib.rs:849-860): p = ray_o + ray_d * z (un-normalised ray_d), dir = viewdir_unit."""
+    o = np.array(golden["camera_origin"], np.float32)
+    rd = np.array(ex["ray_d"], np.float32)
+    vd = np.array(ex["viewdir_unit"], np.float32)
+    z = np.array(golden["z_vals"], np.float32)
+    pts = (o[:, None] + rd[:, None] * z[None, :]).astype(np.float32)
+    return pts, np.tile(vd, (len(z), 1))
+
+
+def test_loader_sizes(onets):
+    # shapes.txt: 12 kernels + 12 biases, 595 844 params = 2 383 376 B per net (lego_rust/README.md)
+    names = ["dense%d" % i for i in range(8)] + ["bottleneck", "viewdirs", "rgb", "alpha"]
+    for net in onets:
+        total = sum(net.tensor(n + "_kernel").size + net.tensor(n + "_bias").size for n in names)
+        assert total == 595844
+    w = onets[0].tensor("dense5_kernel")
+    raw = np.fromfile(os.path.join(DATA, "coarse", "dense5_kernel.bin"), "<f4")
+    assert w.size == 319 * 256 and (w == raw).all()  # byte-exact, little-endian f32 (lib.rs:35-42)
+
+
+def test_oracle_matches_tf_golden(golden, onets):
+    """The reference's own assertion is |d| < 1e-2 (lib.rs:732-742); the f32 restatement is far inside it."""
+    worst_s = worst_c = 0.0
+    for ex in golden["examples"]:
+        pts, dirs = _example_inputs(golden, ex)
+        for net, key in zip(onets, ("coarse", "fine")):
+            rgb, sig = net.forward_batch(pts, dirs)
+            worst_s = max(worst_s, np.abs(sig - np.array(ex[key + "_sigma"])).max())
+            worst_c = max(worst_c, np.abs(rgb - np.array(ex[key + "_rgb"])).max())
+    assert worst_s < 1e-4 and worst_c < 1e-6, (worst_s, worst_c)
+
+
+def test_literal_loop_order_is_bit_identical(golden, onets):
+    pts, dirs = _example_inputs(golden, golden["examples"][0])
+    a = onets[1].forward_batch(pts, dirs, gemm_order=O.GEMM_REORDERED)
+    b = onets[1].forward_batch(pts, dirs, gemm_order=O.GEMM_LITERAL)
+    assert (a[0] == b[0]).all() and (a[1] == b[1]).all()
+
+
+def test_empty_batch(onets):
+    rgb, sig = onets[0].forward_batch(np.zeros((3, 0), np.float32), np.zeros((0, 3), np.float32))
+    assert rgb.shape == (0, 3) and sig.shape == (0,)
+
+
+def test_ray_dirs_match_json_ray_d(golden, ocam):
+    """JSON pixel = [row, col] of the 400x400 TF image; un-normalised dirs with the pixel-corner offset equal ray_d."""
+    for ex in golden["examples"]:
+        i, j = ex["pixel"]
+        d = O.ray_dirs(ocam, 400, 400, offset=0.0, normalize=False, ray_begin=i * 400 + j, ray_end=i * 400 + j + 1)
+        assert np.abs(d[0] - np.array(ex["ray_d"])).max() < 5e-7
+    d = O.ray_dirs(ocam, 8, 8)
+    assert np.allclose(np.linalg.norm(d, axis=1), 1.0, atol=1e-6)
+
+
+def test_stratified_det(ocam):
+    t = O.stratified(2.0, 6.0, 64, np.full(64, 0.5, np.float32))
+    assert np.allclose(t, 2.0 + (np.arange(64) + 0.5) * 0.0625, atol=1e-6)
+    assert (np.diff(t) > 0).all()
+
+
+def test_compute_weights_closed_form():
+    n, far = 64, 6.0
+    t = np.linspace(2.0, 6.0, n, endpoint=False).astype(np.float32)
+    w = O.compute_weights(np.full(n, 0.7, np.float32), t, far)
+    a = 1 - np.exp(-0.7 * 0.0625)
+    assert np.allclose(w, (1 - a) ** np.arange(n) * a, rtol=2e-5)
+    # early exit (lib.rs:276-279): everything after T < 1e-4 is exactly zero, the crossing sample keeps its weight
+    w = O.compute_weights(np.full(n, 100.0, np.float32), t, far)
+    assert w[0] > 0.99 and w[1] > 0 and (w[2:] == 0).all()
+    # negative delta clamps to 0 (lib.rs:267-269)
+    w = O.compute_weights(np.ones(3, np.float32), np.array([3, 2, 4], np.float32), far)
+    assert w[0] == 0.0
+
+
+def test_sample_importance_semantics():
+    n = 64
+    t = (2.0 + (np.arange(n) + 0.5) * 0.0625).astype(np.float32)
+    w = np.zeros(n, np.float32)
+    w[20] = 1.0
+    u = ((np.arange(128) + 0.5) / 128).astype(np.float32)
+    s = O.sample_importance(t, w, u)
+    assert len(s) == 128 and (np.diff(s) >= 0).all()
+    inside = (s >= 0.5 * (t[19] + t[20])) & (s <= 0.5 * (t[20] + t[21]))
+    assert inside.mean() > 0.99  # nearly all mass in bin 19 of the 62 bins
+    assert len(O.sample_importance(t[:2], w[:2], u)) == 0  # n < 3 (lib.rs:295-297)
+    assert len(O.sample_importance(t, w, u[:0])) == 0      # count == 0
+    # u at the top of the range falls in the last bin through the forced cdf[last] = 1 (lib.rs:326-328)
+    s = O.sample_importance(t, np.ones(n, np.float32), np.array([0.0, 0.99999994], np.float32))
+    assert abs(s[0] - 0.5 * (t[0] + t[1])) < 1e-6 and s[1] <= 0.5 * (t[-2] + t[-1]) + 1e-6
+
+
+def test_integrate_ray_white_background():
+    t = np.linspace(2, 6, 8, endpoint=False).astype(np.float32)
+    out = O.integrate_ray(np.zeros((8, 3), np.float32), np.zeros(8, np.float32), t, 6.0)
+    assert (out == 1.0).all()  # empty space -> white (lib.rs:194)
+    out = O.integrate_ray(np.full((8, 3), 0.25, np.float32), np.full(8, 1e4, np.float32), t, 6.0)
+    assert np.allclose(out, 0.25, atol=1e-6)
+    assert (O.integrate_ray(np.zeros((0, 3)), np.zeros(0), np.zeros(0), 6.0) == 0).all()  # lib.rs:178-180
+
+
+def test_render_arg_checks(onets, ocam):
+    with pytest.raises(ValueError, match="width must be multiple"):
+        O.render(onets[0], onets[1], ocam, 12, 8, 4, 4)
+    with pytest.raises(ValueError, match="height must be multiple"):
+        O.render(onets[0], onets[1], ocam, 8, 12, 4, 4)
+    with pytest.raises(ValueError, match="greater than 0"):
+        O.render(onets[0], onets[1], ocam, 8, 8, 0, 4)
+
+
+def test_render_range_equals_full_and_stages(onets, ocam):
+    full, st = O.render(onets[0], onets[1], ocam, 8, 8, 8, 8, stages=True)
+    part = O.render(onets[0], onets[1], ocam, 8, 8, 8, 8, ray_begin=13, ray_end=41)
+    assert (part == full[13:41]).all()
+    assert (np.diff(st["t_f"], axis=1) >= 0).all() and st["t_f"].shape == (64, 16)
+    ph = O.render(onets[0], onets[1], ocam, 8, 8, 8, 8, mode=O.SAMPLING_PHILOX, seed=7)
+    ph2 = O.render(onets[0], onets[1], ocam, 8, 8, 8, 8, mode=O.SAMPLING_PHILOX, seed=7, ray_begin=8, ray_end=16)
+    assert (ph2 == ph[8:16]).all() and not (ph == full).all()
+
+
+def test_philox_known_answer():
+    # Philox4x32-10 known-answer vector (Random123 kat_vectors): counter = key = 0
+    u = O.philox_uniforms(0, 0, 0, 4)
+    want = np.array([0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8], np.uint64)
+    assert (u == ((want >> 8).astype(np.float32) / np.float32(16777216.0))).all()
+
+
+def test_ppm_byte_exact(tmp_path):
+    W, H = 16, 8
+    g = np.linspace(-0.2, 1.2, W * H * 3, dtype=np.float32).reshape(H * W, 3)
+    g[3, 1] = np.nan
+    p = tmp_path / "o.ppm"
+    O.save_ppm(str(p), W, H, g)
+    raw = p.read_bytes()
+    head = b"P6\n16 8\n255\n"
+    assert raw.startswith(head) and len(raw) == len(head) + W * H * 3
+    want = np.where(np.isnan(g), 0, np.floor(np.clip(g, 0, 1) * np.float32(255.0) + np.float32(0.5))).astype(np.uint8)
+    assert (np.frombuffer(raw[len(head):], np.uint8) == want.ravel()).all()
+
+
+# --------------------------------------------------------------------------- the product's host side (no GPU)
+def test_abi_exports_every_declared_symbol():
+    import re
+    import nerf_rs_b200 as nb
+    L = nb.lib()
+    hdr = open(os.path.join(os.path.dirname(DATA), "..", "include", "nerf_b200.h")).read()
+    declared = set(re.findall(r"\b(nerf_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(nb.EXPORTS)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert b"sm_100a" in L.nerf_version()
+
+
+def test_host_camera_and_ppm_match_oracle(tmp_path, ocam):
+    import nerf_rs_b200 as nb
+    cam = nb.camera_from_json(CAM_JSON)
+    for a, b in ((cam.origin, ocam.pos), (cam.forward, ocam.dir), (cam.up, ocam.up)):
+        assert list(a) == list(b)
+    assert (cam.alpha_w, cam.alpha_h, cam.near, cam.far) == (ocam.alpha_w, ocam.alpha_h, ocam.near, ocam.far)
+    g = np.random.default_rng(0).uniform(-0.5, 1.5, (64, 3)).astype(np.float32)
+    assert (nb.quantize_rgb8(g) == O.quantize(g)).all()
+    nb.save_ppm(str(tmp_path / "a.ppm"), 8, 8, g)
+    O.save_ppm(str(tmp_path / "b.ppm"), 8, 8, g)
+    assert (tmp_path / "a.ppm").read_bytes() == (tmp_path / "b.ppm").read_bytes()
+    with pytest.raises(nb.NerfError):
+        nb.camera_from_json(str(tmp_path / "missing.json"))
+
+
+def test_no_cpu_fallback():
+    """Without a GPU the product must fail loudly, never compute on the CPU."""
+    import torch
+    import nerf_rs_b200 as nb
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(nb.NerfError) as e:
+        nb.Renderer(DATA)
+    assert e.value.code == -4
+    h = C.c_void_p()
+    assert nb.lib().nerf_create(b"/nonexistent", 0, C.byref(h)) == -2  # NERF_E_IO before touching CUDA
