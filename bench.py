@@ -1,0 +1,280 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark: lego 800x800, 64 coarse + 128 fine samples/ray, rays/s.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--precision fp16|bf16|fp32] [--impl reference]
+
+A step = one full 800x800 frame (640 000 rays, 163.84 M MLP samples) through the whole hot path
+(ray gen -> stratified -> coarse MLP -> importance resampling -> fine MLP -> compositing).
+`value` times it with the frame buffer resident in HBM (nerf_render_device); `e2e` times the public host API
+(pinned host output, D2H inside the timed region).  With N > 1 (torchrun) the frame is split into N contiguous
+pixel-index ranges, one per rank, and gathered to rank 0 over NCCL inside the timed region (strong scaling).
+`--impl reference` times the reference's CPU algorithm (the oracle restatement; the Rust crate cannot be built
+here) on the host cores on a bounded ray sample of the same frame.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W = H = 800
+NC, NF = 64, 128
+FLOP_COARSE = 982528    # sigma-only sample: dense0-7 + alpha
+FLOP_FINE = 1186816     # full-network sample
+WORKLOAD = "lego 800x800, 64 coarse + 128 fine samples/ray, deterministic sampling, tf_reference camera"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("bf16_tflops_sustained", 1404.7), d.get("bf16_tflops", 1653.3), d.get("hbm_gbs", 6538.0), "measured"
+    return 1400.0, 1590.0, 6650.0, "fallback"
+
+
+# ------------------------------------------------------------------------------------------ CPU arm
+def cpu_sample(threads=0, budget_s=15.0):
+    """Times the oracle (reference CPU algorithm, reordered bit-identical GEMM loop) on a middle row band."""
+    from oracle import pyoracle as O
+    import nerf_rs_b200 as nb
+    cam = O.camera_from_json(os.path.join(nb.DATA_ROOT, "tf_reference_samples.json"))
+    oc, of = O.Network(nb.DATA_ROOT + "/coarse"), O.Network(nb.DATA_ROOT + "/fine")
+    cores = O.num_threads() if threads <= 0 else threads
+    begin = (H // 2) * W
+    n0 = 8 * cores  # calibration: one 8-ray strip per thread
+    t0 = time.perf_counter()
+    O.render(oc, of, cam, W, H, NC, NF, ray_begin=begin, ray_end=begin + n0, threads=cores)
+    per_ray = (time.perf_counter() - t0) / n0
+    n = int(max(64, min(W * 8, budget_s / per_ray)) // 8 * 8)
+    return O, (oc, of, cam), cores, begin, n
+
+
+def run_cpu_step(ctx, cores, begin, n):
+    O, (oc, of, cam) = ctx
+    t0 = time.perf_counter()
+    O.render(oc, of, cam, W, H, NC, NF, ray_begin=begin, ray_end=begin + n, threads=cores)
+    return time.perf_counter() - t0
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    O, ctx, cores, begin, n = cpu_sample(budget_s=10.0)
+    for _ in range(min(args.warmup, 1)):
+        run_cpu_step((O, ctx), cores, begin, n)
+    times = [run_cpu_step((O, ctx), cores, begin, n) for _ in range(args.steps)]
+    dt = float(np.mean(times))
+    val = n / dt
+    sample = f"{n} rays (pixel indices {begin}..{begin + n}) of the 800x800 frame per step, 256 MLP samples/ray"
+    print(json.dumps({
+        "impl": "reference", "metric": "rays/s", "value": val, "unit": "rays/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": sample},
+        "samples_per_s": val * (NC + NC + NF),
+        "cpu_baseline": {"value": val, "unit": "rays/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ------------------------------------------------------------------------------------------ GPU arm
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.path = f"/tmp/bench_clocks_{os.getpid()}.csv"
+        try:
+            self.f = open(self.path, "w")
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 7:
+                continue
+            try:
+                sm.append(float(c[0]))
+                mx.append(float(c[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, c[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.path)
+        if sm:
+            busy = [x for x in sm if x > 0.5 * max(sm)] or sm
+            out = {"sm_mhz": float(np.median(busy)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                   "samples": len(sm)}
+        return out
+
+
+def gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    import nerf_rs_b200 as nb
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: libnerf_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    r = nb.Renderer(nb.DATA_ROOT, device=local)
+    cam = nb.camera_from_json(os.path.join(nb.DATA_ROOT, "tf_reference_samples.json"))
+    n_rays = W * H
+    rb, re_ = rank * n_rays // world, (rank + 1) * n_rays // world
+    n_local = re_ - rb
+    counts = [(k + 1) * n_rays // world - k * n_rays // world for k in range(world)]
+    frame = torch.empty((n_rays, 3), dtype=torch.float32, device=dev)  # rank 0 assembles the frame here
+    mine = frame[rb:re_] if world == 1 else torch.empty((n_local, 3), dtype=torch.float32, device=dev)
+    pinned = torch.empty((n_rays, 3), dtype=torch.float32).pin_memory()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream()
+
+    def gather():
+        if world == 1:
+            return
+        if rank == 0:
+            parts = [frame[sum(counts[:k]):sum(counts[:k + 1])] for k in range(world)]
+            dist.gather(mine, parts, dst=0)
+        else:
+            dist.gather(mine, None, dst=0)
+
+    def step_device():
+        r.render_device(cam, W, H, mine.data_ptr(), NC, NF, precision=args.precision, ray_begin=rb, ray_end=re_,
+                        stream=stream.cuda_stream)
+        gather()
+
+    def step_e2e():
+        if world == 1:
+            r.render_image(cam, W, H, NC, NF, precision=args.precision, out=pinned.numpy())  # host API, syncs
+        else:
+            step_device()
+            if rank == 0:
+                pinned.copy_(frame, non_blocking=True)
+            stream.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k, use_events):
+        """K steps, L2 flushed (untimed) before each one; returns summed step time in ms (max over ranks)."""
+        tot = 0.0
+        mlp_c = mlp_f = smp = comp = 0.0
+        for _ in range(k):
+            flush.zero_()
+            barrier()
+            if use_events:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                fn()
+                e1.record(stream)
+                torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1)
+                tm = r.timing()  # CUDA events recorded by the library on the same stream around each kernel
+                mlp_c += tm["mlp_coarse_ms"]; mlp_f += tm["mlp_fine_ms"]; smp += tm["sampling_ms"]; comp += tm["composite_ms"]
+            else:
+                t0 = time.perf_counter()
+                fn()
+                torch.cuda.synchronize()
+                ms = (time.perf_counter() - t0) * 1e3
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            tot += float(t.item())
+        return tot, (mlp_c / k, mlp_f / k, smp / k, comp / k)
+
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    clocks = ClockSampler(local) if rank == 0 else None
+    total_ms, (mc, mf, sm_ms, cp_ms) = timed(step_device, args.steps, True)
+    clk = clocks.stop() if clocks else {}
+    step_e2e()
+    e2e_ms, _ = timed(step_e2e, args.steps, False)
+
+    if rank == 0:
+        import ctypes
+        h2d_bytes = ctypes.sizeof(nb.Camera) + ctypes.sizeof(nb.Sampling)  # the only per-step input: the pose
+        ms = total_ms / args.steps
+        value = n_rays / (ms * 1e-3)
+        e2e_val = n_rays / (e2e_ms / args.steps * 1e-3)
+        sustained, burst, hbm, kind = load_peaks()
+        fine_flop = n_local * (NC + NF) * FLOP_FINE  # rank 0's fine-pass launch (the dominant kernel)
+        ach = fine_flop / (mf * 1e-3) / 1e12
+        line = {
+            "metric": "rays/s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+            "config": {"workload": WORKLOAD, "precision": args.precision, "parallelism": f"ray-range x{world}",
+                       "l2": "flushed (256 MiB memset, untimed) before every step; per-frame intermediates ~3 GB >> 126 MB L2",
+                       "gather": "NCCL gather of rgb ranges to rank 0 inside the timed region" if world > 1 else "none"},
+            "samples_per_s": value * (NC + NC + NF),
+            "tflops_frame": n_rays * (NC * FLOP_COARSE + (NC + NF) * FLOP_FINE) / (ms * 1e-3) / 1e12 ,
+            "stage_ms_rank0": {"mlp_coarse": mc, "mlp_fine": mf, "sampling": sm_ms, "composite": cp_ms},
+            "gpu_launches": 5 * args.steps,
+            "clocks": clk,
+            "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": h2d_bytes,
+                    "d2h_bytes_per_step": n_rays * 12},
+            "roofline": {"bound": "tensor", "kernel": "mlp_tc_kernel (fine pass)", "achieved": ach, "peak": sustained,
+                         "unit": "TFLOP/s", "frac": ach / sustained, "peak_kind": f"bf16 sustained, {kind}",
+                         "frac_of_burst": ach / burst, "traffic": None},
+        }
+        if world == 1 and not args.no_cpu:
+            O, ctx, cores, begin, n = cpu_sample()
+            dt = run_cpu_step((O, ctx), cores, begin, n)
+            line["cpu_baseline"] = {"value": n / dt, "unit": "rays/s", "cores": cores, "kind": "port",
+                                    "sample": f"{n} rays of the same frame (pixel indices {begin}..{begin + n}), "
+                                              f"{dt:.1f} s, oracle reordered bit-identical GEMM loop"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    r.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--precision", default="fp16", choices=["fp16", "bf16", "fp32"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()
