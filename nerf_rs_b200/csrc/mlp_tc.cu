@@ -12,10 +12,13 @@
 //     the same D.  concat_rows(bottleneck, PE4(dir)) (network.rs:220) likewise (K = 256 + 32).
 //   - sigma (256 -> 1) and rgb (128 -> 3) heads are f32 dot products in the epilogue on the f32 accumulators.
 // Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warp 2 = TMEM allocator,
-// warps 4..7 = epilogue of slot X, warps 8..11 = epilogue of slot Y (warp % 4 = its TMEM lane quadrant).
+// warps 4..11 = epilogue of slot X, warps 12..19 = epilogue of slot Y (warp % 4 = TMEM lane quadrant, two warps
+// per quadrant split the 256 columns).
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -26,7 +29,8 @@ namespace nerf {
 namespace {
 
 constexpr int kTileM = 128;
-constexpr int kThreads = 384;
+constexpr int kThreads = 640;            // 4 control warps + 16 epilogue warps
+constexpr int kEpiThreadsPerSlot = 256;  // 8 warps: 4 TMEM lane quadrants x 2 column halves
 constexpr int kStages = 2;
 constexpr uint32_t kChunkK = 64;                 // K elements per weight chunk (one 128-byte swizzle row)
 constexpr uint32_t kStageBytes = 256 * 128;      // [256 x 64] 16-bit
@@ -41,7 +45,11 @@ constexpr uint32_t kSmemBytes = kOffBar + 128 + 1024;  // + barriers + slack for
 
 // Layer table: chunks per layer in consumption order.
 constexpr int kNumLayers = 10;  // dense0..7, bottleneck, viewdirs
-__host__ __device__ constexpr int layer_chunks(int l) { return l == 0 ? 1 : ((l == 5 || l == 9) ? 5 : 4); }
+// Bias rides on the tensor core: the aux tile carries a constant-1 column (k = 63 of PE10(p), k = 31 of PE4(dir))
+// and the matching weight row holds the layer's bias.  dense0 / dense5 / viewdirs have a PE chunk anyway; every
+// other layer starts with a "bias chunk" (only row k = 63 non-zero) of which a single K16 step is issued.
+__host__ __device__ constexpr int layer_chunks(int l) { return l == 0 ? 1 : 5; }
+__host__ __device__ constexpr bool layer_has_bias_chunk(int l) { return l != 0 && l != 5 && l != 9; }
 __host__ __device__ constexpr int layer_n(int l) { return l == 9 ? 128 : 256; }
 
 // ------------------------------------------------------------------------------------------ PTX wrappers
@@ -102,6 +110,37 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
       : "r"(taddr)
       : "memory");
 }
+// Warp-uniform roles keep all 32 lanes in the loop; only the elected lane issues TMA / MMA / commit.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+// sin and cos of |x| < ~1e4 (PE arguments stay below 2^9 * |p| ~ 3.1e3): three-constant Cody-Waite reduction by
+// pi/2 and the usual degree-7/8 minimax polynomials on [-pi/4, pi/4]; abs error ~2e-7, no slow path, no stack.
+__device__ __forceinline__ void fast_sincos(float x, float& s, float& c) {
+  const float j = rintf(x * 0.636619772f);
+  float r = fmaf(j, -1.57079601e+00f, x);
+  r = fmaf(j, -3.13916473e-07f, r);
+  r = fmaf(j, -5.39030253e-15f, r);
+  const int q = (int)j;
+  const float r2 = r * r;
+  float sp = fmaf(r2, -1.95152959e-4f, 8.33216087e-3f);
+  sp = fmaf(sp, r2, -1.66666546e-1f);
+  sp = fmaf(sp * r2, r, r);
+  float cp = fmaf(r2, 2.44331571e-5f, -1.38873163e-3f);
+  cp = fmaf(cp, r2, 4.16666418e-2f);
+  cp = fmaf(cp, r2, -0.5f);
+  cp = fmaf(cp, r2, 1.0f);
+  const float ss = (q & 1) ? cp : sp;
+  const float cc = (q & 1) ? sp : cp;
+  s = (q & 2) ? -ss : ss;
+  c = ((q + 1) & 2) ? -cc : cc;
+}
 __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
@@ -146,20 +185,23 @@ __device__ __forceinline__ uint16_t cvt1(float v) {
 
 
 // ------------------------------------------------------------------------------------------ epilogue pieces
-// One 32-column block of a layer's accumulator for this thread's row: D -> +bias -> (ReLU) -> 16-bit -> A tile.
-// kSigma additionally accumulates the f32 sigma head on the unrounded ReLU outputs.
+// A 256-wide layer is drained by 8 warps per tile slot: warp (quad, half) owns TMEM lanes 32*quad..+31
+// (one sample row per thread) and columns 128*half..+127, as four 32-column blocks.  TMEM loads are software
+// pipelined: block b+1 is in flight while block b is converted and stored.
+// One 32-column block of the accumulator (bias already inside, see layer_has_bias_chunk): optional sigma
+// partial on the unrounded f32 values; optional ReLU + 16-bit store into the next layer's A tile.
 template <bool kFp16, bool kRelu, bool kSigma, bool kStore>
-__device__ __forceinline__ void epi_block(uint32_t taddr, const float* __restrict__ bias, const float* __restrict__ walpha,
-                                          float& sig, uint8_t* act_row /* A tile + row offset */, uint32_t r8, int cb) {
-  uint32_t v[32];
-  tc_ld32(taddr + cb * 32, v);
-  tc_wait_ld();
-  float x[32];
-#pragma unroll
-  for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]) + bias[cb * 32 + j];
+__device__ __forceinline__ void epi_block(const uint32_t (&v)[32], const float* __restrict__ walpha, float& sig,
+                                          uint8_t* act_row, uint32_t r8, int cb) {
   if constexpr (kSigma) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) sig = fmaf(fmaxf(x[j], 0.0f), walpha[cb * 32 + j], sig);
+    for (int j = 0; j < 32; j += 4) {
+      const float4 w = __ldg(reinterpret_cast<const float4*>(walpha + cb * 32 + j));
+      sig = fmaf(fmaxf(__uint_as_float(v[j]), 0.0f), w.x, sig);
+      sig = fmaf(fmaxf(__uint_as_float(v[j + 1]), 0.0f), w.y, sig);
+      sig = fmaf(fmaxf(__uint_as_float(v[j + 2]), 0.0f), w.z, sig);
+      sig = fmaf(fmaxf(__uint_as_float(v[j + 3]), 0.0f), w.w, sig);
+    }
   }
   if constexpr (kStore) {
     uint8_t* kblock = act_row + (cb >> 1) * kKBlockBytes;
@@ -167,46 +209,75 @@ __device__ __forceinline__ void epi_block(uint32_t taddr, const float* __restric
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       uint4 q;
-      q.x = pack2<kFp16, kRelu>(x[i * 8 + 0], x[i * 8 + 1]);
-      q.y = pack2<kFp16, kRelu>(x[i * 8 + 2], x[i * 8 + 3]);
-      q.z = pack2<kFp16, kRelu>(x[i * 8 + 4], x[i * 8 + 5]);
-      q.w = pack2<kFp16, kRelu>(x[i * 8 + 6], x[i * 8 + 7]);
+      q.x = pack2<kFp16, kRelu>(__uint_as_float(v[i * 8 + 0]), __uint_as_float(v[i * 8 + 1]));
+      q.y = pack2<kFp16, kRelu>(__uint_as_float(v[i * 8 + 2]), __uint_as_float(v[i * 8 + 3]));
+      q.z = pack2<kFp16, kRelu>(__uint_as_float(v[i * 8 + 4]), __uint_as_float(v[i * 8 + 5]));
+      q.w = pack2<kFp16, kRelu>(__uint_as_float(v[i * 8 + 6]), __uint_as_float(v[i * 8 + 7]));
       *reinterpret_cast<uint4*>(kblock + (((chunk0 + i) ^ r8) << 4)) = q;
     }
   }
 }
 
+// Four 32-column blocks starting at block cb0, TMEM loads double-buffered.
 template <bool kFp16, bool kRelu, bool kSigma, bool kStore>
-__device__ __forceinline__ void epi_layer(uint32_t taddr, const float* __restrict__ bias,
-                                          const float* __restrict__ walpha, float& sig, uint8_t* act_row, uint32_t r8) {
-#pragma unroll 1
-  for (int cb = 0; cb < 8; ++cb) epi_block<kFp16, kRelu, kSigma, kStore>(taddr, bias, walpha, sig, act_row, r8, cb);
+__device__ __forceinline__ void epi_layer(uint32_t taddr, const float* __restrict__ walpha, float& sig,
+                                          uint8_t* act_row, uint32_t r8, int cb0) {
+  uint32_t va[32], vb[32];
+  tc_ld32(taddr + cb0 * 32, va);
+  tc_ld32(taddr + (cb0 + 1) * 32, vb);
+  tc_wait_ld();
+  epi_block<kFp16, kRelu, kSigma, kStore>(va, walpha, sig, act_row, r8, cb0);
+  tc_ld32(taddr + (cb0 + 2) * 32, va);
+  epi_block<kFp16, kRelu, kSigma, kStore>(vb, walpha, sig, act_row, r8, cb0 + 1);
+  tc_ld32(taddr + (cb0 + 3) * 32, vb);
+  tc_wait_ld();
+  epi_block<kFp16, kRelu, kSigma, kStore>(va, walpha, sig, act_row, r8, cb0 + 2);
+  epi_block<kFp16, kRelu, kSigma, kStore>(vb, walpha, sig, act_row, r8, cb0 + 3);
 }
 
-// positional_encoding_* (network.rs:263-330) of one sample into row `row` of a [128 x 64] aux tile.
+// positional_encoding_* (network.rs:263-330): octaves [o0, o1) of one sample into row `row` of an aux tile.
 template <bool kFp16>
-__device__ __forceinline__ void write_encoding(uint8_t* aux, uint32_t row, const float v[3], int octaves, int pad_to) {
-#pragma unroll
-  for (int a = 0; a < 3; ++a) *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, a)) = cvt1<kFp16>(v[a]);
+__device__ __forceinline__ void write_octaves(uint8_t* aux, uint32_t row, const float v[3], int o0, int o1) {
 #pragma unroll 1
-  for (int o = 0; o < octaves; ++o) {
+  for (int o = o0; o < o1; ++o) {
     const float f = (float)(1 << o);  // f doubles per octave (network.rs:287)
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
       float sv, cv;
-      sincosf(f * v[a], &sv, &cv);
+      fast_sincos(f * v[a], sv, cv);
       *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, 3 + 6 * o + a)) = cvt1<kFp16>(sv);
       *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, 6 + 6 * o + a)) = cvt1<kFp16>(cv);
     }
   }
-  for (int k = 3 + 6 * octaves; k < pad_to; ++k) *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, k)) = 0;
 }
+template <bool kFp16>
+__device__ __forceinline__ void write_raw3(uint8_t* aux, uint32_t row, const float v[3]) {
+#pragma unroll
+  for (int a = 0; a < 3; ++a) *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, a)) = cvt1<kFp16>(v[a]);
+}
+// Developer timeline (NERF_B200_TRACE=<file>): CTA 0 records (tag, clock64) pairs per role; null in production.
+constexpr int kTraceCap = 2048;
+struct Tracer {
+  unsigned long long* p;
+  int n;
+  __device__ __forceinline__ void rec(uint32_t tag) {
+    if (p != nullptr && n < kTraceCap) {
+      p[2 * n] = tag;
+      p[2 * n + 1] = (unsigned long long)clock64();
+      ++n;
+    }
+  }
+};
+__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
 
 // ------------------------------------------------------------------------------------------ the kernel
 template <bool kFp16>
 __global__ void __launch_bounds__(kThreads, 1)
-mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ chunks, const SampleSrc src,
-              const SampleDst dst) {
+mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunks, const SampleSrc src,
+              const SampleDst dst, unsigned long long* __restrict__ trace) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B atoms need 1 KiB alignment
@@ -228,7 +299,7 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_acc + 8 * s, 1);
-      mbar_init(bar_act + 8 * s, kTileM);
+      mbar_init(bar_act + 8 * s, kEpiThreadsPerSlot);
     }
     fence_barrier_init();
   }
@@ -244,16 +315,22 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
 
   if (warp == 0) {
     // ===================================================== TMA producer: stream weight chunks through the ring
-    if (lane == 0) {
+    {
+      Tracer tr{(trace != nullptr && blockIdx.x == 0 && lane == 0) ? trace + 1 * 2 * kTraceCap : nullptr, 0};
       uint32_t stage = 0, phase = 0;
       for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
         const uint8_t* src_ptr = chunks;
         for (int l = 0; l < n_layers; ++l) {
           const uint32_t bytes = (uint32_t)layer_n(l) * 128u;
           for (int c = 0; c < layer_chunks(l); ++c) {
+            tr.rec(0x100 | l);
             mbar_wait(bar_empty + 8 * stage, phase ^ 1u);
-            mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
-            tma_bulk_g2s(base + kOffStage + stage * kStageBytes, src_ptr, bytes, bar_full + 8 * stage);
+            tr.rec(0x200 | l);
+            if (elect_one()) {
+              mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
+              tma_bulk_g2s(base + kOffStage + stage * kStageBytes, src_ptr, bytes, bar_full + 8 * stage);
+            }
+            __syncwarp();
             src_ptr += bytes;
             if (++stage == kStages) { stage = 0; phase ^= 1u; }
           }
@@ -262,54 +339,74 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
     }
   } else if (warp == 1) {
     // ===================================================== MMA issuer: one thread drives the tensor core
-    if (lane == 0) {
+    {
+      Tracer tr{(trace != nullptr && blockIdx.x == 0 && lane == 0) ? trace : nullptr, 0};
       uint32_t stage = 0, phase = 0, act_par[2] = {0u, 0u};
       for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
         const int n_active = (2 * pair + 1 < n_tiles) ? 2 : 1;
         for (int l = 0; l < n_layers; ++l) {
           const uint32_t idesc = make_idesc(kFp16 ? 1 : 0, layer_n(l));
-          for (int s = 0; s < n_active; ++s) {
-            mbar_wait(bar_act + 8 * s, act_par[s]);
-            act_par[s] ^= 1u;
-          }
-          tc_fence_after();
           const int nch = layer_chunks(l);
           for (int c = 0; c < nch; ++c) {
+            tr.rec(0x100 | (l << 4) | c);
             mbar_wait(bar_full + 8 * stage, phase);
+            tr.rec(0x200 | (l << 4) | c);
             tc_fence_after();
-            const bool from_aux = (l == 0) || (l == 5 && c == 0) || (l == 9 && c == 4);
-            const int ksteps = (l == 9 && c == 4) ? 2 : 4;  // PE4(dir): 27 rows padded to K = 32
-            const int kb = (l == 5) ? c - 1 : c;
+            const bool bias_chunk = layer_has_bias_chunk(l) && c == 0;
+            const bool from_aux = bias_chunk || (l == 0) || (l == 5 && c == 0) || (l == 9 && c == 4);
+            const int ks0 = bias_chunk ? 3 : 0;             // bias chunk: only the K16 step holding the ones column
+            const int ks1 = (l == 9 && c == 4) ? 2 : 4;     // PE4(dir): 27 rows + ones column, padded to K = 32
+            const int kb = (l == 9) ? c : c - 1;
             const uint32_t b_addr = base + kOffStage + stage * kStageBytes;
             for (int s = 0; s < n_active; ++s) {
+              if (c == 0) {  // this slot's input operand (and drained accumulator) for layer l
+                mbar_wait(bar_act + 8 * s, act_par[s]);
+                act_par[s] ^= 1u;
+                tc_fence_after();
+                tr.rec(0x300 | (l << 4) | s);
+              }
               const uint32_t a_addr =
                   from_aux ? base + kOffAux + s * kAuxBytes : base + kOffAct + s * kActBytes + kb * kKBlockBytes;
               const uint32_t d_tmem = tmem_base + (uint32_t)s * 256u;
-              for (int ks = 0; ks < ksteps; ++ks)
-                tc_mma_f16(d_tmem, make_desc(a_addr + ks * 32), make_desc(b_addr + ks * 32), idesc,
-                           (c | ks) != 0 ? 1u : 0u);
-              if (c == nch - 1) tc_commit(bar_acc + 8 * s);  // accumulator of this layer complete -> epilogue
+              if (elect_one()) {
+                for (int ks = ks0; ks < ks1; ++ks)
+                  tc_mma_f16(d_tmem, make_desc(a_addr + ks * 32), make_desc(b_addr + ks * 32), idesc,
+                             (c != 0 || ks != ks0) ? 1u : 0u);
+                if (c == nch - 1) tc_commit(bar_acc + 8 * s);  // accumulator of this layer complete -> epilogue
+              }
+              __syncwarp();
             }
-            tc_commit(bar_empty + 8 * stage);  // both slots have consumed the chunk -> producer may refill
+            if (elect_one()) tc_commit(bar_empty + 8 * stage);  // both slots consumed the chunk -> refill allowed
+            __syncwarp();
             if (++stage == kStages) { stage = 0; phase ^= 1u; }
           }
         }
       }
     }
   } else if (warp >= 4) {
-    // ===================================================== epilogue warps: one thread per sample row
-    const int slot = (warp - 4) >> 2;
+    // ===================================================== epilogue warps: one thread per (sample row, column half)
+    const int ew = warp - 4;
+    const int slot = ew >> 3;
+    const int half = (ew >> 2) & 1;
     const uint32_t quad = (uint32_t)(warp & 3);
     const uint32_t row = quad * 32u + (uint32_t)lane;
     const uint32_t r8 = row & 7u;
     const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + (uint32_t)slot * 256u;
     uint8_t* act_row = smem + kOffAct + slot * kActBytes + (row >> 3) * 1024u + r8 * 128u;
     uint8_t* aux = smem + kOffAux + slot * kAuxBytes;
+    // f32 scratch for combining the two column halves of a row: aux columns 32..63 are free whenever it is used
+    float* scratch = reinterpret_cast<float*>(aux + sw128_offset(row, 32));       // sigma partial (16 B chunk)
+    float* scratch2 = reinterpret_cast<float*>(aux + sw128_offset(row, 40));      // rgb partials
+    const uint32_t pair_bar = 1u + (uint32_t)slot * 4u + quad;                    // named barrier of the 2 warps of a row
     const uint32_t acc_bar = bar_acc + 8 * slot, act_bar = bar_act + 8 * slot;
+    const int cb0 = half * 4;
     uint32_t acc_par = 0;
+    Tracer tr{(trace != nullptr && blockIdx.x == 0 && quad == 0 && lane == 0) ? trace + (2 + slot * 2 + half) * 2 * kTraceCap
+                                                                             : nullptr, 0};
     for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
       const int64_t tile = 2 * pair + slot;
       if (tile >= n_tiles) continue;
+      tr.rec(0x500);
       const int64_t g = tile * kTileM + row;
       const bool valid = g < src.B;
       float p[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 0.f};
@@ -332,41 +429,63 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
           p[2] = __fadd_rn(src.origin[2], __fmul_rn(d[2], t));
         }
       }
-      write_encoding<kFp16>(aux, row, p, kPosOctaves, 64);  // layer-0 / skip operand (network.rs:204)
+      // PE10(p): layer-0 / skip operand (network.rs:204); the two halves split the octaves
+      if (half == 0) {
+        write_raw3<kFp16>(aux, row, p);
+        write_octaves<kFp16>(aux, row, p, 0, 5);
+      } else {
+        write_octaves<kFp16>(aux, row, p, 5, 10);
+        *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, 63)) = cvt1<kFp16>(1.0f);  // ones column: bias row
+      }
       fence_proxy_async();
       tc_fence_before();
       mbar_arrive(act_bar);
+      tr.rec(0x400);
 
-      float sig = C.b_alpha;
+      float sig = half == 0 ? __ldg(&Cg->b_alpha) : 0.0f;
 #pragma unroll 1
       for (int l = 0; l < 7; ++l) {
+        tr.rec(0x100 | l);
         mbar_wait(acc_bar, acc_par);
         acc_par ^= 1u;
         tc_fence_after();
-        epi_layer<kFp16, true, false, true>(taddr, C.bias[l], C.w_alpha, sig, act_row, r8);
+        tr.rec(0x200 | l);
+        epi_layer<kFp16, true, false, true>(taddr, Cg->w_alpha, sig, act_row, r8, cb0);
         fence_proxy_async();
         tc_fence_before();
         mbar_arrive(act_bar);
+        tr.rec(0x300 | l);
       }
       mbar_wait(acc_bar, acc_par);  // dense7 -> h8; sigma = relu(alpha(h8)) (network.rs:216)
       acc_par ^= 1u;
       tc_fence_after();
       if (want_rgb) {
-        epi_layer<kFp16, true, true, true>(taddr, C.bias[7], C.w_alpha, sig, act_row, r8);
+        epi_layer<kFp16, true, true, true>(taddr, Cg->w_alpha, sig, act_row, r8, cb0);
         fence_proxy_async();
         tc_fence_before();
         mbar_arrive(act_bar);
       } else {
-        epi_layer<kFp16, true, true, false>(taddr, C.bias[7], C.w_alpha, sig, act_row, r8);
+        epi_layer<kFp16, true, true, false>(taddr, Cg->w_alpha, sig, act_row, r8, cb0);
         tc_fence_before();
       }
-      if (valid) dst.sigma[g] = fmaxf(sig, 0.0f);
+      if (half == 1) scratch[0] = sig;
+      named_bar_sync(pair_bar, 64);
+      if (half == 0 && valid) dst.sigma[g] = fmaxf(sig + scratch[0], 0.0f);
+      named_bar_sync(pair_bar, 64);  // scratch lives in aux columns the other half overwrites next
       if (want_rgb) {
         mbar_wait(acc_bar, acc_par);  // bottleneck, ActivationType::None (network.rs:218)
         acc_par ^= 1u;
         tc_fence_after();
-        epi_layer<kFp16, false, false, true>(taddr, C.bias[8], C.w_alpha, sig, act_row, r8);
-        write_encoding<kFp16>(aux, row, d, kDirOctaves, 32);  // PE4(dir) replaces PE10(p): skip MMA is long done
+        epi_layer<kFp16, false, false, true>(taddr, Cg->w_alpha, sig, act_row, r8, cb0);
+        // PE4(dir) replaces PE10(p) in the aux tile: the skip MMA that read it finished layers ago
+        if (half == 0) {
+          write_raw3<kFp16>(aux, row, d);
+          write_octaves<kFp16>(aux, row, d, 0, 2);
+        } else {
+          write_octaves<kFp16>(aux, row, d, 2, 4);
+          for (int k = kDirEnc; k < 31; ++k) *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, k)) = 0;
+          *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, 31)) = cvt1<kFp16>(1.0f);  // ones column: bias row
+        }
         fence_proxy_async();
         tc_fence_before();
         mbar_arrive(act_bar);
@@ -374,26 +493,39 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
         mbar_wait(acc_bar, acc_par);  // viewdirs (ReLU) then the f32 rgb head + sigmoid (network.rs:222-223)
         acc_par ^= 1u;
         tc_fence_after();
-        float r0 = C.b_rgb[0], r1 = C.b_rgb[1], r2 = C.b_rgb[2];
+        float r0 = 0.f, r1 = 0.f, r2 = 0.f;
+        if (half == 0) { r0 = __ldg(&Cg->b_rgb[0]); r1 = __ldg(&Cg->b_rgb[1]); r2 = __ldg(&Cg->b_rgb[2]); }
 #pragma unroll 1
-        for (int cb = 0; cb < 4; ++cb) {
+        for (int cb = half * 2; cb < half * 2 + 2; ++cb) {
           uint32_t v[32];
           tc_ld32(taddr + cb * 32, v);
           tc_wait_ld();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float cj = fmaxf(__uint_as_float(v[j]) + C.bias[9][cb * 32 + j], 0.0f);
-            r0 = fmaf(cj, C.w_rgb[(cb * 32 + j) * 3 + 0], r0);
-            r1 = fmaf(cj, C.w_rgb[(cb * 32 + j) * 3 + 1], r1);
-            r2 = fmaf(cj, C.w_rgb[(cb * 32 + j) * 3 + 2], r2);
+          for (int j = 0; j < 32; j += 4) {
+            const float4 wa = __ldg(reinterpret_cast<const float4*>(&Cg->w_rgb[(cb * 32 + j) * 3]));
+            const float4 wb = __ldg(reinterpret_cast<const float4*>(&Cg->w_rgb[(cb * 32 + j) * 3 + 4]));
+            const float4 wc = __ldg(reinterpret_cast<const float4*>(&Cg->w_rgb[(cb * 32 + j) * 3 + 8]));
+            const float c0 = fmaxf(__uint_as_float(v[j]), 0.0f), c1 = fmaxf(__uint_as_float(v[j + 1]), 0.0f);
+            const float c2 = fmaxf(__uint_as_float(v[j + 2]), 0.0f), c3 = fmaxf(__uint_as_float(v[j + 3]), 0.0f);
+            r0 = fmaf(c0, wa.x, r0); r1 = fmaf(c0, wa.y, r1); r2 = fmaf(c0, wa.z, r2);
+            r0 = fmaf(c1, wa.w, r0); r1 = fmaf(c1, wb.x, r1); r2 = fmaf(c1, wb.y, r2);
+            r0 = fmaf(c2, wb.z, r0); r1 = fmaf(c2, wb.w, r1); r2 = fmaf(c2, wc.x, r2);
+            r0 = fmaf(c3, wc.y, r0); r1 = fmaf(c3, wc.z, r1); r2 = fmaf(c3, wc.w, r2);
           }
         }
         tc_fence_before();
-        if (valid) {
-          dst.rgb[g * 3 + 0] = 1.0f / (1.0f + expf(-r0));  // network.rs:165
-          dst.rgb[g * 3 + 1] = 1.0f / (1.0f + expf(-r1));
-          dst.rgb[g * 3 + 2] = 1.0f / (1.0f + expf(-r2));
+        if (half == 1) {
+          scratch2[0] = r0;
+          scratch2[1] = r1;
+          scratch2[2] = r2;
         }
+        named_bar_sync(pair_bar, 64);
+        if (half == 0 && valid) {
+          dst.rgb[g * 3 + 0] = 1.0f / (1.0f + expf(-(r0 + scratch2[0])));  // network.rs:165
+          dst.rgb[g * 3 + 1] = 1.0f / (1.0f + expf(-(r1 + scratch2[1])));
+          dst.rgb[g * 3 + 2] = 1.0f / (1.0f + expf(-(r2 + scratch2[2])));
+        }
+        named_bar_sync(pair_bar, 64);  // scratch is inside the aux tile the next tile's PE overwrites
       }
     }
   }
@@ -408,6 +540,7 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
 }  // namespace
 }  // namespace nerf
 
+
 // ============================================================================ host side
 namespace nerf {
 namespace {
@@ -417,23 +550,29 @@ inline uint16_t host_cvt(float v, int fmt) {
 }
 
 // Appends the [n x 64] SWIZZLE_128B image of W rows [k0, k0 + krows) (W is [in][out] row-major, so the B
-// operand element (n, k) is W[k0 + k][n]); rows beyond krows are zero padding.
-void append_chunk(std::vector<uint8_t>& img, const std::vector<float>& W, int out_dim, int k0, int krows, int n,
-                  int fmt) {
+// operand element (n, k) is W[k0 + k][n]); rows beyond krows are zero padding, except row `bias_k` (if >= 0),
+// which holds the layer's bias and meets the ones column of the aux tile.
+void append_chunk(std::vector<uint8_t>& img, const std::vector<float>* W, int out_dim, int k0, int krows, int n,
+                  int fmt, const std::vector<float>* bias, int bias_k) {
   const size_t base = img.size();
   img.resize(base + (size_t)n * 128, 0);
-  for (int row = 0; row < n; ++row)
+  for (int row = 0; row < n; ++row) {
     for (int k = 0; k < krows; ++k) {
-      const uint16_t h = host_cvt(W[(size_t)(k0 + k) * out_dim + row], fmt);
+      const uint16_t h = host_cvt((*W)[(size_t)(k0 + k) * out_dim + row], fmt);
       std::memcpy(&img[base + sw128_offset((uint32_t)row, (uint32_t)k)], &h, 2);
     }
+    if (bias != nullptr) {
+      const uint16_t h = host_cvt((*bias)[row], fmt);
+      std::memcpy(&img[base + sw128_offset((uint32_t)row, (uint32_t)bias_k)], &h, 2);
+    }
+  }
 }
 
 }  // namespace
 
 int build_tc_weights(const TensorMap& t, int fmt, const NetF32&, TcWeights* out) {
   std::vector<uint8_t> img;
-  img.reserve(1200 * 1024);
+  img.reserve(1500 * 1024);
   static const char* const names[10] = {"dense0", "dense1", "dense2", "dense3", "dense4",
                                         "dense5", "dense6", "dense7", "bottleneck", "viewdirs"};
   std::memset(&out->consts, 0, sizeof(out->consts));
@@ -443,15 +582,16 @@ int build_tc_weights(const TensorMap& t, int fmt, const NetF32&, TcWeights* out)
     const int n = layer_n(l);
     for (int o = 0; o < n; ++o) out->consts.bias[l][o] = b[o];
     if (l == 0) {
-      append_chunk(img, W, n, 0, kPosEnc, n, fmt);  // PE10 rows 0..62, k = 63 zero
+      append_chunk(img, &W, n, 0, kPosEnc, n, fmt, &b, 63);  // PE10 rows 0..62, bias at k = 63
     } else if (l == 5) {
-      append_chunk(img, W, n, 0, kPosEnc, n, fmt);  // rows 0..62 multiply h0 (concat_rows(h0, h4), network.rs:210)
-      for (int c = 0; c < 4; ++c) append_chunk(img, W, n, kPosEnc + 64 * c, 64, n, fmt);
+      append_chunk(img, &W, n, 0, kPosEnc, n, fmt, &b, 63);  // rows 0..62 multiply h0 (concat_rows(h0, h4), network.rs:210)
+      for (int c = 0; c < 4; ++c) append_chunk(img, &W, n, kPosEnc + 64 * c, 64, n, fmt, nullptr, 0);
     } else if (l == 9) {
-      for (int c = 0; c < 4; ++c) append_chunk(img, W, n, 64 * c, 64, n, fmt);  // bottleneck FIRST (network.rs:220)
-      append_chunk(img, W, n, kHidden, kDirEnc, n, fmt);                        // then PE4(dir) rows 256..282
+      for (int c = 0; c < 4; ++c) append_chunk(img, &W, n, 64 * c, 64, n, fmt, nullptr, 0);  // bottleneck FIRST (network.rs:220)
+      append_chunk(img, &W, n, kHidden, kDirEnc, n, fmt, &b, 31);  // then PE4(dir) rows 256..282, bias at k = 31
     } else {
-      for (int c = 0; c < 4; ++c) append_chunk(img, W, n, 64 * c, 64, n, fmt);
+      append_chunk(img, nullptr, n, 0, 0, n, fmt, &b, 63);  // bias chunk
+      for (int c = 0; c < 4; ++c) append_chunk(img, &W, n, 64 * c, 64, n, fmt, nullptr, 0);
     }
   }
   const std::vector<float>& wa = t.at("alpha_kernel").data;
@@ -464,6 +604,8 @@ int build_tc_weights(const TensorMap& t, int fmt, const NetF32&, TcWeights* out)
   out->bytes = img.size();
   cudaError_t e = cudaMalloc(&out->d_chunks, img.size());
   if (e == cudaSuccess) e = cudaMemcpy(out->d_chunks, img.data(), img.size(), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMalloc(&out->d_consts, sizeof(TcConsts));
+  if (e == cudaSuccess) e = cudaMemcpy(out->d_consts, &out->consts, sizeof(TcConsts), cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
     set_error(std::string("upload tensor-core weight tiles: ") + cudaGetErrorString(e));
     return NERF_E_CUDA;
@@ -473,7 +615,9 @@ int build_tc_weights(const TensorMap& t, int fmt, const NetF32&, TcWeights* out)
 
 void free_tc_weights(TcWeights* w) {
   if (w->d_chunks) cudaFree(w->d_chunks);
+  if (w->d_consts) cudaFree(w->d_consts);
   w->d_chunks = nullptr;
+  w->d_consts = nullptr;
   w->bytes = 0;
 }
 
@@ -484,16 +628,34 @@ cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const Sample
   const int64_t n_pairs = (n_tiles + 1) / 2;
   const int grid = (int)(n_pairs < sm_count ? n_pairs : sm_count);
   cudaError_t e;
+  unsigned long long* trace = nullptr;
+  const char* trace_path = std::getenv("NERF_B200_TRACE");  // developer timeline, off in production
+  const size_t trace_bytes = 6 * 2 * kTraceCap * sizeof(unsigned long long);
+  if (trace_path != nullptr) {
+    if ((e = cudaMalloc(&trace, trace_bytes)) != cudaSuccess) return e;
+    cudaMemsetAsync(trace, 0, trace_bytes, s);
+  }
   if (w.fmt == 1) {
     e = cudaFuncSetAttribute(mlp_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e != cudaSuccess) return e;
-    mlp_tc_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst);
+    mlp_tc_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(w.d_consts, w.d_chunks, src, dst, trace);
   } else {
     e = cudaFuncSetAttribute(mlp_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e != cudaSuccess) return e;
-    mlp_tc_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst);
+    mlp_tc_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(w.d_consts, w.d_chunks, src, dst, trace);
   }
-  return cudaGetLastError();
+  e = cudaGetLastError();
+  if (trace != nullptr) {
+    std::vector<unsigned long long> h(trace_bytes / 8);
+    cudaStreamSynchronize(s);
+    cudaMemcpy(h.data(), trace, trace_bytes, cudaMemcpyDeviceToHost);
+    cudaFree(trace);
+    if (FILE* f = std::fopen(trace_path, "ab")) {
+      std::fwrite(h.data(), 8, h.size(), f);
+      std::fclose(f);
+    }
+  }
+  return e;
 }
 
 }  // namespace nerf

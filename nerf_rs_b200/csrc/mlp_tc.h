@@ -5,9 +5,9 @@
 
 namespace nerf {
 
-// Small f32 tables the epilogue needs; passed to the kernel as a __grid_constant__ parameter so they
-// are served from the constant bank.
-struct TcConsts {
+// Small f32 tables the epilogue needs; they live in global memory and are read with warp-uniform 16-byte
+// loads (L1 hits), which is cheaper than register-indexed constant-bank loads.
+struct alignas(16) TcConsts {
   float bias[10][256];   // dense0..7, bottleneck, viewdirs (128 used)
   float w_alpha[256];    // sigma head weights (network.rs:216), evaluated in f32 in the epilogue
   float w_rgb[128 * 3];  // rgb head weights [128][3] (network.rs:223)
@@ -20,6 +20,7 @@ struct TcConsts {
 // (N=256: 32 KiB; viewdirs N=128: 16 KiB), so the kernel streams it with a 1-D bulk TMA copy.
 struct TcWeights {
   uint8_t* d_chunks = nullptr;
+  TcConsts* d_consts = nullptr;
   size_t bytes = 0;
   int fmt = 0;  // 0 = bf16, 1 = fp16
   TcConsts consts;
