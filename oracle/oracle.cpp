@@ -78,14 +78,18 @@ struct Layer {
   int in = 0, out = 0;
   std::vector<float> w;  // [in][out] row-major, exactly the .bin contents (network.rs:63, lib.rs:121)
   std::vector<float> b;  // [out]
-  mutable std::vector<float> w_rounded[4];  // built by prepare() before any parallel region
+  mutable std::vector<float> w_rounded[4], b_rounded[4];  // built by prepare() before any parallel region
   void prepare(int mode) const {
     if (mode == ORACLE_ROUND_NONE || !w_rounded[mode].empty()) return;
-    std::vector<float> tmp(w.size());
+    std::vector<float> tmp(w.size()), tb(b.size());
     for (size_t i = 0; i < w.size(); ++i) tmp[i] = round_mode_apply(w[i], mode);
+    for (size_t i = 0; i < b.size(); ++i) tb[i] = round_mode_apply(b[i], mode);
     w_rounded[mode].swap(tmp);
+    b_rounded[mode].swap(tb);
   }
   const float* weights(int mode) const { return mode == ORACLE_ROUND_NONE ? w.data() : w_rounded[mode].data(); }
+  // The tensor-core kernel feeds the bias through the MMA (a ones column), so it is an operand too.
+  const float* bias(int mode) const { return mode == ORACLE_ROUND_NONE ? b.data() : b_rounded[mode].data(); }
 };
 
 enum Act { RELU, SIGMOID, NONE };  // network.rs:67-72
@@ -102,7 +106,8 @@ inline float activate(float v, Act a) {  // network.rs:161-169
 // Reordered variant: per block of 16 columns, i outer / o inner.  Per output element the operation
 // sequence is bias, then +W[0][o]*h[0], +W[1][o]*h[1], ... exactly as the reference's in->col->out
 // loops produce it (each element's partial sums are independent of the others), so it is bit-identical.
-void dense_reordered(const Layer& L, const float* W, const float* h, int64_t B, Act act, float* out) {
+void dense_reordered(const Layer& L, const float* W, const float* bias, const float* h, int64_t B, Act act,
+                     float* out) {
   const int in = L.in, no = L.out;
   constexpr int CB = 16;  // one cache line of activations per input row
   std::vector<float> acc((size_t)CB * no), hb((size_t)in * CB);
@@ -111,7 +116,7 @@ void dense_reordered(const Layer& L, const float* W, const float* h, int64_t B, 
     for (int i = 0; i < in; ++i)
       for (int k = 0; k < cb; ++k) hb[(size_t)i * CB + k] = h[(size_t)i * B + c0 + k];
     for (int k = 0; k < cb; ++k)
-      for (int o = 0; o < no; ++o) acc[(size_t)k * no + o] = L.b[o];
+      for (int o = 0; o < no; ++o) acc[(size_t)k * no + o] = bias[o];
     for (int i = 0; i < in; ++i) {
       const float* __restrict wr = W + (size_t)i * no;
       for (int k = 0; k < cb; ++k) {
@@ -127,10 +132,11 @@ void dense_reordered(const Layer& L, const float* W, const float* h, int64_t B, 
 }
 
 // The reference's literal loop nest (network.rs:134-143): in -> col -> out with strided get/set.
-void dense_literal(const Layer& L, const float* W, const float* h, int64_t B, Act act, float* out) {
+void dense_literal(const Layer& L, const float* W, const float* bias, const float* h, int64_t B, Act act,
+                   float* out) {
   const int in = L.in, no = L.out;
   for (int o = 0; o < no; ++o)
-    for (int64_t c = 0; c < B; ++c) out[(size_t)o * B + c] = L.b[o];
+    for (int64_t c = 0; c < B; ++c) out[(size_t)o * B + c] = bias[o];
   for (int i = 0; i < in; ++i) {
     const float* wr = W + (size_t)i * no;
     for (int64_t c = 0; c < B; ++c) {
@@ -144,11 +150,12 @@ void dense_literal(const Layer& L, const float* W, const float* h, int64_t B, Ac
   for (size_t k = 0; k < (size_t)no * B; ++k) out[k] = activate(out[k], act);
 }
 
-void dense(const Layer& L, const float* W, const float* h, int64_t B, Act act, int order, float* out) {
+// rm selects the operand set: ORACLE_ROUND_NONE is the reference's f32 arithmetic.
+void dense(const Layer& L, int rm, const float* h, int64_t B, Act act, int order, float* out) {
   if (order == ORACLE_GEMM_LITERAL)
-    dense_literal(L, W, h, B, act, out);
+    dense_literal(L, L.weights(rm), L.bias(rm), h, B, act, out);
   else
-    dense_reordered(L, W, h, B, act, out);
+    dense_reordered(L, L.weights(rm), L.bias(rm), h, B, act, out);
 }
 
 // positional_encoding_batch / _dirs (network.rs:263-330): rows [v, sin(f v)x3, cos(f v)x3, ...], f doubled.
@@ -200,7 +207,7 @@ void forward_batch(const oracle_net& N, const float* points, const float* dirs, 
   round_inplace(h0, rm);
   std::vector<float> h = h0, nxt((size_t)256 * B);
   for (int i = 0; i < 5; ++i) {  // network.rs:206-208
-    dense(N.layers[i], N.layers[i].weights(rm), h.data(), B, RELU, order, nxt.data());
+    dense(N.layers[i], rm, h.data(), B, RELU, order, nxt.data());
     h = nxt;
     round_inplace(h, rm);
   }
@@ -210,18 +217,18 @@ void forward_batch(const oracle_net& N, const float* points, const float* dirs, 
   h = cat;
   std::vector<float> h8_f32;
   for (int i = 5; i < 8; ++i) {  // network.rs:211-213
-    dense(N.layers[i], N.layers[i].weights(rm), h.data(), B, RELU, order, nxt.data());
+    dense(N.layers[i], rm, h.data(), B, RELU, order, nxt.data());
     h = nxt;
     if (i == 7) h8_f32 = h;
     round_inplace(h, rm);
   }
   // sigma = relu(alpha(h8))  (network.rs:216): f32 head on the unrounded h8 in every mode.
   std::vector<float> sig((size_t)B);
-  dense(N.alpha, N.alpha.w.data(), h8_f32.data(), B, RELU, order, sig.data());
+  dense(N.alpha, ORACLE_ROUND_NONE, h8_f32.data(), B, RELU, order, sig.data());
   std::memcpy(sigma, sig.data(), sizeof(float) * B);  // row_slice(0) (network.rs:234)
 
   std::vector<float> bn((size_t)256 * B);  // network.rs:218, ActivationType::None
-  dense(N.bottleneck, N.bottleneck.weights(rm), h.data(), B, NONE, order, bn.data());
+  dense(N.bottleneck, rm, h.data(), B, NONE, order, bn.data());
   round_inplace(bn, rm);
   std::vector<float> q((size_t)283 * B);  // concat_rows(bottleneck, PE4(dirs)): bottleneck FIRST (network.rs:219-220)
   std::memcpy(q.data(), bn.data(), sizeof(float) * 256 * B);
@@ -232,8 +239,8 @@ void forward_batch(const oracle_net& N, const float* points, const float* dirs, 
     std::memcpy(q.data() + (size_t)256 * B, dpe.data(), sizeof(float) * 27 * B);
   }
   std::vector<float> ch((size_t)128 * B), cm((size_t)3 * B);
-  dense(N.viewdirs, N.viewdirs.weights(rm), q.data(), B, RELU, order, ch.data());  // network.rs:222
-  dense(N.rgb, N.rgb.w.data(), ch.data(), B, SIGMOID, order, cm.data());           // network.rs:223 (f32 head)
+  dense(N.viewdirs, rm, q.data(), B, RELU, order, ch.data());  // network.rs:222
+  dense(N.rgb, ORACLE_ROUND_NONE, ch.data(), B, SIGMOID, order, cm.data());           // network.rs:223 (f32 head)
   for (int64_t c = 0; c < B; ++c) {  // network.rs:225-232
     rgb[c * 3 + 0] = cm[0 * B + c];
     rgb[c * 3 + 1] = cm[1 * B + c];

@@ -116,7 +116,6 @@ def test_compute_weights(renderer):
         # 1e-6 are excluded: 1 - expf(-tiny) is 0 or 6e-8 depending on the last ulp of expf.
         big = np.maximum(np.abs(want), np.abs(got)) > 1e-6
         assert ((want == 0) == (got == 0))[big].all()
-        cut = np.cumprod(1.0 - want.astype(np.float64).clip(0, 1), axis=1)  # rays that reached the cut-off
         assert (got[want == 0] < 1e-6).all()
 
 
