@@ -32,7 +32,6 @@ constexpr int kTileM = 128;
 constexpr int kThreads = 640;            // 4 control warps + 16 epilogue warps
 constexpr int kEpiThreadsPerSlot = 256;  // 8 warps: 4 TMEM lane quadrants x 2 column halves
 constexpr int kStages = 2;
-constexpr uint32_t kChunkK = 64;                 // K elements per weight chunk (one 128-byte swizzle row)
 constexpr uint32_t kStageBytes = 256 * 128;      // [256 x 64] 16-bit
 constexpr uint32_t kKBlockBytes = kTileM * 128;  // one [128 x 64] K-block of an A tile
 constexpr uint32_t kActBytes = 4 * kKBlockBytes; // [128 x 256]
@@ -75,7 +74,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "=r"(done)
         : "r"(bar), "r"(parity)
         : "memory");
-    if (spins > (1u << 26)) __trap();
+    if (spins > (1u << 22)) __trap();  // ~0.2 s: far beyond any legitimate wait
   }
 }
 __device__ __forceinline__ void tma_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
@@ -286,7 +285,9 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
   const uint32_t bar_full = bar0, bar_empty = bar0 + 16, bar_acc = bar0 + 32, bar_act = bar0 + 48;  // 2 x 8 B each
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kOffBar + 64);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // Broadcast through a shuffle so that the compiler knows the warp index is warp-uniform: role branches then
+  // are uniform branches and the MMA issuer's descriptors live in uniform registers (no R2UR per MMA).
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const bool want_rgb = dst.rgb != nullptr;
   const int n_layers = want_rgb ? kNumLayers : 8;
   const int64_t n_tiles = (src.B + kTileM - 1) / kTileM;
@@ -368,10 +369,18 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
               const uint32_t a_addr =
                   from_aux ? base + kOffAux + s * kAuxBytes : base + kOffAct + s * kActBytes + kb * kKBlockBytes;
               const uint32_t d_tmem = tmem_base + (uint32_t)s * 256u;
+              // Descriptors are built once per chunk; a K16 step only advances the start-address field (+32 B = +2).
+              const uint64_t ad = make_desc(a_addr), bd = make_desc(b_addr);
               if (elect_one()) {
-                for (int ks = ks0; ks < ks1; ++ks)
-                  tc_mma_f16(d_tmem, make_desc(a_addr + ks * 32), make_desc(b_addr + ks * 32), idesc,
-                             (c != 0 || ks != ks0) ? 1u : 0u);
+                if (ks0 == 0 && ks1 == 4) {
+                  tc_mma_f16(d_tmem, ad, bd, idesc, c != 0 ? 1u : 0u);
+                  tc_mma_f16(d_tmem, ad + 2, bd + 2, idesc, 1u);
+                  tc_mma_f16(d_tmem, ad + 4, bd + 4, idesc, 1u);
+                  tc_mma_f16(d_tmem, ad + 6, bd + 6, idesc, 1u);
+                } else {
+                  for (int ks = ks0; ks < ks1; ++ks)
+                    tc_mma_f16(d_tmem, ad + 2 * ks, bd + 2 * ks, idesc, (c != 0 || ks != ks0) ? 1u : 0u);
+                }
                 if (c == nch - 1) tc_commit(bar_acc + 8 * s);  // accumulator of this layer complete -> epilogue
               }
               __syncwarp();
