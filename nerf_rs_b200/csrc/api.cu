@@ -254,7 +254,7 @@ int check_render_args(const nerf_ctx* c, const nerf_camera* cam, int W, int H, i
     set_error("n_fine > 0 needs n_coarse >= 3 (ragged rays are not supported)");
     return NERF_E_UNSUPPORTED;
   }
-  if ((size_t)(6 * (size_t)nc + nf) * 8 * sizeof(float) > 200 * 1024) {
+  if ((size_t)(6 * (size_t)nc + 2 * (size_t)nf) * 2 * 8 * sizeof(float) > 200 * 1024) {  // pow2 padding <= 2x
     set_error("n_coarse/n_fine too large for the importance sampler's shared memory");
     return NERF_E_UNSUPPORTED;
   }

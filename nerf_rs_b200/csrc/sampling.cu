@@ -99,8 +99,55 @@ __device__ __forceinline__ float warp_weights_round(const float* sig, const floa
   return (t_before < 1e-4f) ? 0.0f : t_before * alpha;  // lib.rs:272-279
 }
 
-// K3: coarse weights -> pdf -> cdf -> inverse-CDF samples -> merge with coarse t -> stable sort.
-// Per-warp shared memory: t[nc] w[nc] pdf[nc] cdf[nc] bins[nc] merged[nc+nf].
+// ---- sorting helpers of K3.  sort_by(partial_cmp) (lib.rs:419) is a stable sort of plain floats: equal floats
+// are indistinguishable, so ANY ascending arrangement of the multiset is bit-identical to the reference's.
+__host__ __device__ inline int next_pow2(int n) {
+  int p = 1;
+  while (p < n) p <<= 1;
+  return p;
+}
+// Warp-cooperative bitonic sort of a[0..p) in shared memory, p a power of two (padding = +inf).
+__device__ __forceinline__ void warp_bitonic_sort(float* a, int p, int lane) {
+  for (int k = 2; k <= p; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = lane; i < (p >> 1); i += 32) {
+        const int lo = ((i & ~(j - 1)) << 1) | (i & (j - 1));  // i-th index with bit j clear
+        const int hi = lo | j;
+        const bool up = (lo & k) == 0;
+        const float x = a[lo], y = a[hi];
+        if ((x > y) == up) {
+          a[lo] = y;
+          a[hi] = x;
+        }
+      }
+      __syncwarp();
+    }
+  }
+}
+// true iff a[0..n) is non-decreasing (warp-uniform result)
+__device__ __forceinline__ bool warp_is_sorted(const float* a, int n, int lane) {
+  bool ok = true;
+  for (int i = lane; i + 1 < n; i += 32) ok = ok && !(a[i + 1] < a[i]);
+  return __all_sync(kFull, ok);
+}
+// number of elements of the ascending array a[0..n) that are < v (strict) or <= v
+__device__ __forceinline__ int count_less(const float* a, int n, float v, bool or_equal) {
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    const float x = a[mid];
+    if (or_equal ? (x <= v) : (x < v)) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo;
+}
+
+// K3: coarse weights -> pdf -> cdf -> inverse-CDF samples -> merge with coarse t -> sort.  One warp per ray.
+// Per-warp shared memory: t[nc] w[nc] pdf[nc] cdf[nc] bins[nc] fine[pow2(nf)] (+ coarse copy [pow2(nc)] only if the
+// caller's coarse samples are not ascending).
+// Rounding-sensitive steps keep the reference's operation order: the pdf sum and the cdf prefix sum are sequential
+// f32 folds (lib.rs:310,319-328); every lane evaluates the same fold from broadcast shared-memory reads, which
+// costs no more than one lane doing it and needs no broadcast afterwards.
 __global__ void __launch_bounds__(kWarpsPerCta * 32) importance_kernel(
     const float* __restrict__ tc, const float* __restrict__ sigc, const float* __restrict__ w_in, int nc, int nf,
     float far_, int mode, uint64_t seed,
@@ -109,22 +156,20 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) importance_kernel(
   extern __shared__ float smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nm = nc + nf;
-  float* s_t = smem + (size_t)warp * (5 * nc + nm);
+  const int pf = next_pow2(nf > 0 ? nf : 1), pc = next_pow2(nc);
+  float* s_t = smem + (size_t)warp * (5 * nc + pf + pc);
   float* s_w = s_t + nc;
   float* s_pdf = s_w + nc;
   float* s_cdf = s_pdf + nc;
   float* s_bins = s_cdf + nc;
-  float* s_m = s_bins + nc;
+  float* s_f = s_bins + nc;   // fine samples, padded to pf with +inf
+  float* s_c = s_f + pf;      // sorted copy of the coarse samples (only used when they arrive unsorted)
   const int m = nc - 2;  // pdf_weights = weights[1..n-1] (lib.rs:299)
 
   for (int64_t ray = blockIdx.x * (int64_t)kWarpsPerCta + warp; ray < n_rays; ray += (int64_t)gridDim.x * kWarpsPerCta) {
     const float* tr = tc + ray * nc;
     const float* sr = sigc + ray * nc;
-    for (int i = lane; i < nc; i += 32) {
-      const float tv = tr[i];
-      s_t[i] = tv;
-      s_m[i] = tv;  // merged = coarse_ts.clone() (lib.rs:416)
-    }
+    for (int i = lane; i < nc; i += 32) s_t[i] = tr[i];
     __syncwarp();
     if (w_in != nullptr) {
       for (int i = lane; i < nc; i += 32) s_w[i] = w_in[ray * nc + i];
@@ -139,58 +184,81 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) importance_kernel(
       }
     }
     __syncwarp();
+    float* out = tf + ray * nm;
     if (nf > 0) {
       for (int i = lane; i < m; i += 32) s_pdf[i] = fmaxf(s_w[i + 1], 0.0f) + 1e-5f;  // lib.rs:309
       for (int i = lane; i < nc - 1; i += 32) s_bins[i] = 0.5f * (s_t[i] + s_t[i + 1]);  // lib.rs:286
       __syncwarp();
       float sum = 0.0f;
-      if (lane == 0)
-        for (int i = 0; i < m; ++i) sum += s_pdf[i];  // sequential fold, as iter().sum() (lib.rs:310)
-      sum = __shfl_sync(kFull, sum, 0);
+      for (int i = 0; i < m; ++i) sum += s_pdf[i];  // sequential fold, as iter().sum() (lib.rs:310)
+      // cdf[i+1] = cdf[i] + pdf[i] / sum, sequentially (lib.rs:315-328); lane i % 32 keeps element i + 1
       for (int i = lane; i < m; i += 32) s_pdf[i] = s_pdf[i] / sum;  // lib.rs:315-317
       __syncwarp();
-      if (lane == 0) {  // sequential prefix sum keeps the reference's rounding of every bin edge (lib.rs:319-328)
-        float cum = 0.0f;
-        s_cdf[0] = 0.0f;
-        for (int i = 0; i < m; ++i) {
-          cum += s_pdf[i];
-          s_cdf[i + 1] = cum;
-        }
-        s_cdf[m] = 1.0f;
+      float cum = 0.0f;
+      if (lane == 0) s_cdf[0] = 0.0f;
+      for (int i = 0; i < m; ++i) {
+        cum += s_pdf[i];
+        if ((i & 31) == lane) s_cdf[i + 1] = cum;
       }
+      __syncwarp();
+      if (lane == 0) s_cdf[m] = 1.0f;  // lib.rs:327
       __syncwarp();
       const int64_t pixel = ray_begin + ray;
-      for (int k = lane; k < nf; k += 32) {
-        float uu;
-        if (mode == NERF_SAMPLING_DET) uu = ((float)k + 0.5f) / (float)nf;
-        else if (mode == NERF_SAMPLING_PHILOX) uu = philox_uniform(seed, (uint32_t)pixel, 1u, k);
-        else uu = u_in[ray * nf + k];
-        int idx = m - 1;  // lib.rs:333
-        for (int j = 0; j < m; ++j) {
-          if (uu >= s_cdf[j] && uu < s_cdf[j + 1]) {  // first match (lib.rs:334-339)
-            idx = j;
-            break;
+      for (int k = lane; k < pf; k += 32) {
+        float v = __int_as_float(0x7f800000);  // +inf padding for the sort
+        if (k < nf) {
+          float uu;
+          if (mode == NERF_SAMPLING_DET) uu = ((float)k + 0.5f) / (float)nf;
+          else if (mode == NERF_SAMPLING_PHILOX) uu = philox_uniform(seed, (uint32_t)pixel, 1u, k);
+          else uu = u_in[ray * nf + k];
+          // lib.rs:333-339 picks the first j with cdf[j] <= u < cdf[j+1], default m - 1.  By induction the first j with
+          // u < cdf[j+1] already satisfies cdf[j] <= u, so idx = min{j : u < cdf[j+1]}; cdf[1..m-1] is a running sum of
+          // positive terms (non-decreasing), so that is a binary search; j = m - 1 is both the last candidate and
+          // the default.  NaN compares false everywhere and falls through to m - 1, as in the reference.
+          int lo = 0, hi = m - 1;
+          while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (uu < s_cdf[mid + 1]) hi = mid;
+            else lo = mid + 1;
           }
+          const int idx = lo;
+          const float cl = s_cdf[idx], ch = s_cdf[idx + 1];
+          const float denom = fmaxf(ch - cl, 1e-6f);  // lib.rs:343
+          const float bl = s_bins[idx], bu = s_bins[idx + 1];
+          const float tt = (uu - cl) / denom;
+          v = bl + (bu - bl) * tt;  // lib.rs:347
         }
-        const float lo = s_cdf[idx], hi = s_cdf[idx + 1];
-        const float denom = fmaxf(hi - lo, 1e-6f);  // lib.rs:343
-        const float bl = s_bins[idx], bu = s_bins[idx + 1];
-        const float tt = (uu - lo) / denom;
-        s_m[nc + k] = bl + (bu - bl) * tt;  // lib.rs:347
+        s_f[k] = v;
       }
       __syncwarp();
-    }
-    // Stable sort of merged[nm] (sort_by partial_cmp, lib.rs:419) by ranking: every element counts the
-    // elements that precede it.  All lanes read the same s_m[j] (broadcast), no bank conflicts.
-    float* out = tf + ray * nm;
-    for (int e = lane; e < nm; e += 32) {
-      const float v = s_m[e];
-      int rank = 0;
-      for (int j = 0; j < nm; ++j) {
-        const float o = s_m[j];
-        rank += (o < v || (o == v && j < e)) ? 1 : 0;
+      // merged = coarse ++ fine; sort (lib.rs:416-420).  Both parts are normally ascending already (stratified
+      // samples; inverse CDF of ascending u); otherwise each is sorted on its own, then merged by rank.
+      if (!warp_is_sorted(s_f, nf, lane)) warp_bitonic_sort(s_f, pf, lane);
+      const float* cs = s_t;
+      if (!warp_is_sorted(s_t, nc, lane)) {
+        for (int i = lane; i < pc; i += 32) s_c[i] = i < nc ? s_t[i] : __int_as_float(0x7f800000);
+        __syncwarp();
+        warp_bitonic_sort(s_c, pc, lane);
+        cs = s_c;
       }
-      out[rank] = v;
+      // rank of coarse i = i + #{fine < v}; rank of fine k = k + #{coarse <= v}: a permutation of 0..nm-1
+      for (int i = lane; i < nc; i += 32) {
+        const float v = cs[i];
+        out[i + count_less(s_f, nf, v, false)] = v;
+      }
+      for (int k = lane; k < nf; k += 32) {
+        const float v = s_f[k];
+        out[k + count_less(cs, nc, v, true)] = v;
+      }
+    } else {
+      if (!warp_is_sorted(s_t, nc, lane)) {
+        for (int i = lane; i < pc; i += 32) s_c[i] = i < nc ? s_t[i] : __int_as_float(0x7f800000);
+        __syncwarp();
+        warp_bitonic_sort(s_c, pc, lane);
+        for (int i = lane; i < nc; i += 32) out[i] = s_c[i];
+      } else {
+        for (int i = lane; i < nc; i += 32) out[i] = s_t[i];
+      }
     }
     __syncwarp();
   }
@@ -249,6 +317,10 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) composite_kernel(const floa
   }
 }
 
+size_t importance_smem_bytes(int nc, int nf) {
+  return (size_t)kWarpsPerCta * (5 * (size_t)nc + next_pow2(nf > 0 ? nf : 1) + next_pow2(nc)) * sizeof(float);
+}
+
 inline int grid_for(int64_t work_items, int per_cta) {
   int64_t g = (work_items + per_cta - 1) / per_cta;
   const int64_t cap = 148 * 16;  // 16 resident CTAs of 256 threads would oversubscribe; loops stride the rest
@@ -277,7 +349,7 @@ cudaError_t launch_importance(const float* d_tc, const float* d_sigc, const floa
                               int mode, uint64_t seed, const float* d_u, int64_t ray_begin, int64_t n_rays, float* d_tf,
                               float* d_wc, cudaStream_t s) {
   if (n_rays == 0) return cudaSuccess;
-  const size_t smem = (size_t)kWarpsPerCta * (5 * (size_t)nc + nc + nf) * sizeof(float);
+  const size_t smem = importance_smem_bytes(nc, nf);
   if (smem > 200 * 1024) return cudaErrorInvalidValue;
   cudaError_t e = cudaFuncSetAttribute(importance_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
