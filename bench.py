@@ -147,10 +147,10 @@ def gpu_arm(args):
         dist.init_process_group("nccl", device_id=dev)
     r = nb.Renderer(nb.DATA_ROOT, device=local)
     cam = nb.camera_from_json(os.path.join(nb.DATA_ROOT, "tf_reference_samples.json"))
+    from nerf_rs_b200 import shard
     n_rays = W * H
-    rb, re_ = rank * n_rays // world, (rank + 1) * n_rays // world
+    rb, re_ = shard.ray_range(rank, world, n_rays)
     n_local = re_ - rb
-    counts = [(k + 1) * n_rays // world - k * n_rays // world for k in range(world)]
     frame = torch.empty((n_rays, 3), dtype=torch.float32, device=dev)  # rank 0 assembles the frame here
     mine = frame[rb:re_] if world == 1 else torch.empty((n_local, 3), dtype=torch.float32, device=dev)
     pinned = torch.empty((n_rays, 3), dtype=torch.float32).pin_memory()
@@ -158,13 +158,7 @@ def gpu_arm(args):
     stream = torch.cuda.current_stream()
 
     def gather():
-        if world == 1:
-            return
-        if rank == 0:
-            parts = [frame[sum(counts[:k]):sum(counts[:k + 1])] for k in range(world)]
-            dist.gather(mine, parts, dst=0)
-        else:
-            dist.gather(mine, None, dst=0)
+        shard.gather_frame(mine, frame if rank == 0 else None, rank, world, dist)
 
     def step_device():
         r.render_device(cam, W, H, mine.data_ptr(), NC, NF, precision=args.precision, ray_begin=rb, ray_end=re_,
@@ -236,7 +230,7 @@ def gpu_arm(args):
             "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
             "config": {"workload": WORKLOAD, "precision": args.precision, "parallelism": f"ray-range x{world}",
                        "l2": "flushed (256 MiB memset, untimed) before every step; per-frame intermediates ~3 GB >> 126 MB L2",
-                       "gather": "NCCL gather of rgb ranges to rank 0 inside the timed region" if world > 1 else "none"},
+                       "gather": "NCCL point-to-point group: every rank sends its rgb range to rank 0, inside the timed region" if world > 1 else "none"},
             "samples_per_s": value * (NC + NC + NF),
             "tflops_frame": n_rays * (NC * FLOP_COARSE + (NC + NF) * FLOP_FINE) / (ms * 1e-3) / 1e12 ,
             "stage_ms_rank0": {"mlp_coarse": mc, "mlp_fine": mf, "sampling": sm_ms, "composite": cp_ms},
