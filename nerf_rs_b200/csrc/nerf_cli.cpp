@@ -1,0 +1,97 @@
+// nerf_cli — the reference's command line (src/main.rs:1-3 -> render_cli_image, src/lib.rs:647-677) over the C ABI.
+//
+// With no arguments it does what `cargo run --release` does: loads lego_rust/{coarse,fine}, takes the camera from
+// lego_rust/tf_reference_samples.json, renders 256x256 with 64 coarse + 128 fine samples per ray
+// (default_sample_counts, lib.rs:603-612; width/height lib.rs:657-658), prints the same progress lines and writes
+// output.ppm (save_ppm, lib.rs:567-580).  The flags only expose what the reference hard-codes.
+//
+// The reference jitters samples with an OS-seeded thread_rng (lib.rs:375,407); the default here is the seeded
+// Philox stream (--seed), --det selects the deterministic mid-point sampling used by the parity tests.
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/nerf_b200.h"
+
+namespace {
+
+void usage() {
+  std::printf(
+      "usage: nerf_cli [--weights DIR] [--camera JSON] [--width W] [--height H] [--nc N] [--nf N]\n"
+      "                [--precision fp32|bf16|fp16|tf32] [--det | --seed S] [--device D] [--out FILE]\n"
+      "defaults reproduce the reference CLI: 256x256, 64 coarse + 128 fine samples, output.ppm\n");
+}
+
+int fail(const char* what) {
+  std::fprintf(stderr, "nerf_cli: %s: %s\n", what, nerf_last_error());
+  return 1;
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  std::string root = "lego_rust", cam_path, out = "output.ppm";
+  if (const char* e = std::getenv("NERF_B200_WEIGHTS")) root = e;
+  int W = 256, H = 256, nc = 64, nf = 128, precision = NERF_PREC_FP16, device = 0;
+  nerf_sampling smp{};
+  smp.mode = NERF_SAMPLING_PHILOX;
+  smp.seed = 0;
+  for (int i = 1; i < argc; ++i) {
+    const std::string a = argv[i];
+    auto next = [&](const char* name) -> const char* {
+      if (i + 1 >= argc) {
+        std::fprintf(stderr, "nerf_cli: %s needs a value\n", name);
+        std::exit(2);
+      }
+      return argv[++i];
+    };
+    if (a == "--weights") root = next("--weights");
+    else if (a == "--camera") cam_path = next("--camera");
+    else if (a == "--width") W = std::atoi(next("--width"));
+    else if (a == "--height") H = std::atoi(next("--height"));
+    else if (a == "--nc") nc = std::atoi(next("--nc"));
+    else if (a == "--nf") nf = std::atoi(next("--nf"));
+    else if (a == "--device") device = std::atoi(next("--device"));
+    else if (a == "--out") out = next("--out");
+    else if (a == "--det") smp.mode = NERF_SAMPLING_DET;
+    else if (a == "--seed") { smp.mode = NERF_SAMPLING_PHILOX; smp.seed = std::strtoull(next("--seed"), nullptr, 10); }
+    else if (a == "--precision") {
+      const std::string p = next("--precision");
+      if (p == "fp32") precision = NERF_PREC_FP32;
+      else if (p == "bf16") precision = NERF_PREC_BF16;
+      else if (p == "fp16") precision = NERF_PREC_FP16;
+      else if (p == "tf32") precision = NERF_PREC_TF32;
+      else { std::fprintf(stderr, "nerf_cli: unknown precision %s\n", p.c_str()); return 2; }
+    } else if (a == "--help" || a == "-h") { usage(); return 0; }
+    else { std::fprintf(stderr, "nerf_cli: unknown argument %s\n", a.c_str()); usage(); return 2; }
+  }
+  if (cam_path.empty()) cam_path = root + "/tf_reference_samples.json";  // lib.rs:653-654
+
+  nerf_camera cam;
+  if (nerf_camera_from_json(cam_path.c_str(), &cam) != NERF_OK) return fail("camera");  // lib.rs:665
+  nerf_ctx* ctx = nullptr;
+  if (nerf_create(root.c_str(), device, &ctx) != NERF_OK) return fail("load networks");  // lib.rs:651-652
+
+  std::printf("Rendering with %d coarse samples and %d fine samples per ray\n", nc, nf);  // lib.rs:660-663
+  std::printf("Starting image rendering...\n");                                            // lib.rs:667
+  std::vector<float> rgb((size_t)W * H * 3);
+  const auto t0 = std::chrono::steady_clock::now();  // the reference times render_image only (lib.rs:668-670)
+  if (nerf_render(ctx, &cam, W, H, nc, nf, precision, &smp, 0, (int64_t)W * H, rgb.data()) != NERF_OK) {
+    nerf_destroy(ctx);
+    return fail("render");
+  }
+  const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  std::printf("Rendering complete: %lld/%lld pixels (100.0%%)\n", (long long)W * H, (long long)W * H);  // lib.rs:559-562
+  std::printf("Rendering completed in %.2f seconds\n", secs);  // lib.rs:671-675
+  nerf_timing tm{};
+  if (nerf_get_timing(ctx, &tm) == NERF_OK)
+    std::printf("device time %.3f ms (coarse MLP %.3f, fine MLP %.3f, sampling %.3f, compositing %.3f)\n", tm.total_ms,
+                tm.mlp_coarse_ms, tm.mlp_fine_ms, tm.sampling_ms, tm.composite_ms);
+  nerf_destroy(ctx);
+  if (nerf_save_ppm(out.c_str(), W, H, rgb.data()) != NERF_OK) return fail("save ppm");  // lib.rs:676
+  std::printf("Wrote %s\n", out.c_str());
+  return 0;
+}

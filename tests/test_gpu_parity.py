@@ -205,3 +205,26 @@ def test_render_argument_errors(renderer, cam):
             renderer.render_image(cam, W, H, nc, 4)
         assert e.value.code == -1
     assert renderer.render_image(cam, 8, 8, 4, 4, ray_begin=5, ray_end=5).shape == (0, 3)
+
+
+def test_cli_writes_the_same_ppm(renderer, cam, tmp_path):
+    """nerf_cli (main.rs / render_cli_image, lib.rs:647-677) == the library path, byte for byte, and within the
+    north-star image bound of the oracle's PPM quantisation."""
+    import os
+    import subprocess
+    import nerf_rs_b200 as nb
+    cli = os.path.join(os.path.dirname(nb.LIB_PATH), "nerf_cli")
+    out = tmp_path / "cli.ppm"
+    r = subprocess.run([cli, "--weights", nb.DATA_ROOT, "--width", "32", "--height", "24", "--det", "--precision",
+                        "fp32", "--out", str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "Rendering completed in" in r.stdout and "Starting image rendering..." in r.stdout
+    img = renderer.render_image(cam, 32, 24, 64, 128, precision="fp32")
+    want = b"P6\n32 24\n255\n" + nb.quantize_rgb8(img).tobytes()
+    assert out.read_bytes() == want
+    # reference defaults: 256x256, 64 + 128 samples, output.ppm in the working directory (lib.rs:603-612,657-658,676)
+    r = subprocess.run([cli, "--weights", nb.DATA_ROOT], capture_output=True, text=True, cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    data = (tmp_path / "output.ppm").read_bytes()
+    assert data.startswith(b"P6\n256 256\n255\n") and len(data) == 15 + 256 * 256 * 3
+    assert "Rendering with 64 coarse samples and 128 fine samples per ray" in r.stdout

@@ -191,3 +191,20 @@ def test_no_cpu_fallback():
     assert e.value.code == -4
     h = C.c_void_p()
     assert nb.lib().nerf_create(b"/nonexistent", 0, C.byref(h)) == -2  # NERF_E_IO before touching CUDA
+
+
+def test_cli_builds_and_fails_loudly_without_gpu(tmp_path):
+    """nerf_cli mirrors main.rs / render_cli_image (src/lib.rs:647-677); without a GPU it must fail, not fall back."""
+    import subprocess
+    import nerf_rs_b200 as nb
+    cli = os.path.join(os.path.dirname(nb.LIB_PATH), "nerf_cli")
+    assert os.path.exists(cli), "run __graft_entry__.build()"
+    assert subprocess.run([cli, "--help"], capture_output=True).returncode == 0
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("GPU present: covered by the gpu test")
+    except ImportError:
+        pass
+    r = subprocess.run([cli, "--weights", DATA, "--out", str(tmp_path / "o.ppm")], capture_output=True, text=True)
+    assert r.returncode != 0 and "no CPU fallback" in r.stderr and not (tmp_path / "o.ppm").exists()
