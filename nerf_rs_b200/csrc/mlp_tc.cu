@@ -1,17 +1,23 @@
 // mlp_tc.cu — Network::forward_batch (src/network.rs:197-237) as ONE fused persistent tcgen05 kernel.
 //
-// One CTA per SM processes pairs of 128-sample tiles (slot X, slot Y).  Samples sit on the 128 TMEM lanes
-// (M = 128); every 256-wide layer is a D[128 x 256] += A[128 x K] * B[K x 256] chain of tcgen05.mma
-// (kind::f16, M128 N256 K16) accumulating f32 in TMEM (slot X: columns 0..255, slot Y: 256..511).
-//   - A (activations) never leaves the SM: the epilogue reads D with tcgen05.ld, adds the bias, applies ReLU,
-//     rounds to fp16/bf16 and writes the next layer's A operand straight into shared memory in the K-major
+// A cluster of two CTAs (one CTA per SM, the two SMs of a TPC) works as a pair with tcgen05.mma.cta_group::2:
+// every MMA is M = 256 (128 samples on the TMEM lanes of each CTA) x N = 256 x K = 16, kind::f16, f32 accumulate in
+// TMEM.  A pair processes "quads" of four 128-sample tiles as two slots (slot X: TMEM columns 0..255, slot Y:
+// 256..511); each slot spans both CTAs.
+//   - A (activations) never leaves the SM: the epilogue reads D with tcgen05.ld, applies ReLU, rounds to fp16/bf16
+//     and writes the next layer's A operand straight into its own CTA's shared memory in the K-major
 //     SWIZZLE_128B layout the MMA descriptor expects.
-//   - B (weights) is streamed from L2 as pre-swizzled [N x 64] chunks by 1-D bulk TMA copies through a 2-stage
-//     mbarrier ring; both tile slots consume a chunk before it is released, halving L2 -> SMEM traffic.
+//   - B (weights) is split by N between the two CTAs: each CTA streams only its [N/2 x 64] half of every chunk
+//     (16 KiB) from L2 with 1-D bulk TMA copies, so the 64 KiB ring is four chunks deep (it was two with
+//     cta_group::1) and L2 -> SMEM traffic per SM is halved again.  Both slots consume a chunk before it is released.
+//   - The four-deep ring is what lets the two slots run out of step: the leader's MMA thread advances slot X and slot
+//     Y independently (Y at least two chunks behind X while X can run), so one slot's epilogue overlaps the other
+//     slot's MMAs instead of idling the tensor pipe at every layer boundary.
 //   - concat_rows(h0, h4) (network.rs:210) is split-K: the PE tile (K = 64) and h4 (K = 256) accumulate into
 //     the same D.  concat_rows(bottleneck, PE4(dir)) (network.rs:220) likewise (K = 256 + 32).
 //   - sigma (256 -> 1) and rgb (128 -> 3) heads are f32 dot products in the epilogue on the f32 accumulators.
-// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warp 2 = TMEM allocator,
+// Warp roles (both CTAs): warp 0 = TMA producer of the CTA's weight halves, warp 1 = MMA issuer (leader CTA only,
+// one elected lane), warp 2 = TMEM allocator, warp 3 = relay ("my half of chunk g has landed" -> leader),
 // warps 4..11 = epilogue of slot X, warps 12..19 = epilogue of slot Y (warp % 4 = TMEM lane quadrant, two warps
 // per quadrant split the 256 columns).
 #include <cuda_bf16.h>
@@ -31,8 +37,8 @@ namespace {
 constexpr int kTileM = 128;
 constexpr int kThreads = 640;            // 4 control warps + 16 epilogue warps
 constexpr int kEpiThreadsPerSlot = 256;  // 8 warps: 4 TMEM lane quadrants x 2 column halves
-constexpr int kStages = 2;
-constexpr uint32_t kStageBytes = 256 * 128;      // [256 x 64] 16-bit
+constexpr int kStages = 4;
+constexpr uint32_t kStageBytes = 128 * 128;      // this CTA's N-half of a chunk: [128 x 64] 16-bit
 constexpr uint32_t kKBlockBytes = kTileM * 128;  // one [128 x 64] K-block of an A tile
 constexpr uint32_t kActBytes = 4 * kKBlockBytes; // [128 x 256]
 constexpr uint32_t kAuxBytes = kKBlockBytes;     // [128 x 64]: PE10(p) for layers 0/5, later PE4(dir)
@@ -40,7 +46,10 @@ constexpr uint32_t kOffAct = 0;
 constexpr uint32_t kOffAux = kOffAct + 2 * kActBytes;
 constexpr uint32_t kOffStage = kOffAux + 2 * kAuxBytes;
 constexpr uint32_t kOffBar = kOffStage + kStages * kStageBytes;
-constexpr uint32_t kSmemBytes = kOffBar + 128 + 1024;  // + barriers + slack for manual 1 KiB alignment
+// barrier block, 8 B each: full[4] pfull[4] empty[4] acc[2] act[2]
+constexpr uint32_t kBarFull = 0, kBarPFull = 32, kBarEmpty = 64, kBarAcc = 96, kBarAct = 112, kTmemSlotOff = 128;
+constexpr uint32_t kSmemBytes = kOffBar + 256 + 1024;  // + barriers + slack for manual 1 KiB alignment
+constexpr int kSkew = 2;  // slot Y trails slot X by at least this many chunks while X can advance
 
 // Layer table: chunks per layer in consumption order.
 constexpr int kNumLayers = 10;  // dense0..7, bottleneck, viewdirs
@@ -88,6 +97,54 @@ __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence:
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// ---- CTA-pair (cta_group::2) forms; PTX as in CUTLASS (cutlass/arch/barrier.h, cute/arch/mma_sm100_umma.hpp)
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// Arrive on the barrier at the same shared-memory offset in CTA `cta` of the cluster.  Relaxed: the data the signal
+// guards is only ever read through the async proxy of the SM that wrote it (each SM's tensor core reads its own
+// A tile; TMA wrote the B halves), and the writer already issued fence.proxy.async; a release at cluster scope
+// costs ~1.5k cycles per arrive here.
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) {
+  asm volatile(
+      "{\n\t.reg .b32 remote;\n\t"
+      "mapa.shared::cluster.u32 remote, %0, %1;\n\t"
+      "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [remote];\n\t}" ::"r"(bar),
+      "r"(cta)
+      : "memory");
+}
+// one non-blocking probe of a barrier phase (arrivals may come from the peer CTA)
+__device__ __forceinline__ bool mbar_test_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.relaxed.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(done)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return done != 0;
+}
+// commit: one arrive on the barrier at this offset in BOTH CTAs of the pair once all prior MMAs have completed
+__device__ __forceinline__ void tc_commit2(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+               "h"((uint16_t)3)
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma2_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
 }
 __device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                            uint32_t accumulate) {
@@ -152,8 +209,8 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
 // Instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 [4,6)=1; a/b format [7,10),[10,13):
 // 0 = F16, 1 = BF16; a/b major K (0); N>>3 at [17,23); M>>4 at [24,29).
 __host__ __device__ constexpr uint32_t make_idesc(int fmt_is_fp16, int n) {
-  const uint32_t f = fmt_is_fp16 ? 0u : 1u;
-  return (1u << 4) | (f << 7) | (f << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+  const uint32_t f = fmt_is_fp16 ? 0u : 1u;  // M = 256: the CTA pair (cta_group::2)
+  return (1u << 4) | (f << 7) | (f << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)((2 * kTileM) >> 4) << 24);
 }
 
 // Byte offset of element (row, k) inside a [rows x 64] 16-bit K-major SWIZZLE_128B tile:
@@ -183,6 +240,19 @@ __device__ __forceinline__ uint16_t cvt1(float v) {
 }
 
 
+// Developer timeline (NERF_B200_TRACE=<file>): CTA 0 records (tag, clock64) pairs per role; null in production.
+constexpr int kTraceCap = 2048;
+struct Tracer {
+  unsigned long long* p;
+  int n;
+  __device__ __forceinline__ void rec(uint32_t tag) {
+    if (p != nullptr && n < kTraceCap) {
+      p[2 * n] = tag;
+      p[2 * n + 1] = (unsigned long long)clock64();
+      ++n;
+    }
+  }
+};
 // ------------------------------------------------------------------------------------------ epilogue pieces
 // A 256-wide layer is drained by 8 warps per tile slot: warp (quad, half) owns TMEM lanes 32*quad..+31
 // (one sample row per thread) and columns 128*half..+127, as four 32-column blocks.  TMEM loads are software
@@ -219,17 +289,19 @@ __device__ __forceinline__ void epi_block(const uint32_t (&v)[32], const float* 
 
 // Four 32-column blocks starting at block cb0, TMEM loads double-buffered.
 template <bool kFp16, bool kRelu, bool kSigma, bool kStore>
-__device__ __forceinline__ void epi_layer(uint32_t taddr, const float* __restrict__ walpha, float& sig,
+__device__ __forceinline__ void epi_layer(Tracer& tr, uint32_t taddr, const float* __restrict__ walpha, float& sig,
                                           uint8_t* act_row, uint32_t r8, int cb0) {
   uint32_t va[32], vb[32];
   tc_ld32(taddr + cb0 * 32, va);
   tc_ld32(taddr + (cb0 + 1) * 32, vb);
   tc_wait_ld();
+  tr.rec(0x600);
   epi_block<kFp16, kRelu, kSigma, kStore>(va, walpha, sig, act_row, r8, cb0);
   tc_ld32(taddr + (cb0 + 2) * 32, va);
   epi_block<kFp16, kRelu, kSigma, kStore>(vb, walpha, sig, act_row, r8, cb0 + 1);
   tc_ld32(taddr + (cb0 + 3) * 32, vb);
   tc_wait_ld();
+  tr.rec(0x700);
   epi_block<kFp16, kRelu, kSigma, kStore>(va, walpha, sig, act_row, r8, cb0 + 2);
   epi_block<kFp16, kRelu, kSigma, kStore>(vb, walpha, sig, act_row, r8, cb0 + 3);
 }
@@ -254,27 +326,24 @@ __device__ __forceinline__ void write_raw3(uint8_t* aux, uint32_t row, const flo
 #pragma unroll
   for (int a = 0; a < 3; ++a) *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, a)) = cvt1<kFp16>(v[a]);
 }
-// Developer timeline (NERF_B200_TRACE=<file>): CTA 0 records (tag, clock64) pairs per role; null in production.
-constexpr int kTraceCap = 2048;
-struct Tracer {
-  unsigned long long* p;
-  int n;
-  __device__ __forceinline__ void rec(uint32_t tag) {
-    if (p != nullptr && n < kTraceCap) {
-      p[2 * n] = tag;
-      p[2 * n + 1] = (unsigned long long)clock64();
-      ++n;
-    }
-  }
-};
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
 
 // ------------------------------------------------------------------------------------------ the kernel
+// Position of a slot's MMA stream: chunk c of layer l of the pair's q-th quad; g counts chunks since kernel start
+// (ring stage = g % kStages, ring phase = (g / kStages) & 1).
+struct Stream {
+  int64_t quad;
+  int l, c;
+  uint32_t g;
+  uint32_t act_par;
+  bool done;
+};
+
 template <bool kFp16>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunks, const SampleSrc src,
               const SampleDst dst, unsigned long long* __restrict__ trace) {
   extern __shared__ uint8_t smem_raw[];
@@ -282,114 +351,147 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
   const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B atoms need 1 KiB alignment
   uint8_t* smem = smem_raw + (base - raw);
   const uint32_t bar0 = base + kOffBar;
-  const uint32_t bar_full = bar0, bar_empty = bar0 + 16, bar_acc = bar0 + 32, bar_act = bar0 + 48;  // 2 x 8 B each
-  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kOffBar + 64);
+  const uint32_t bar_full = bar0 + kBarFull, bar_pfull = bar0 + kBarPFull, bar_empty = bar0 + kBarEmpty,
+                 bar_acc = bar0 + kBarAcc, bar_act = bar0 + kBarAct;
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kOffBar + kTmemSlotOff);
 
   // Broadcast through a shuffle so that the compiler knows the warp index is warp-uniform: role branches then
   // are uniform branches and the MMA issuer's descriptors live in uniform registers (no R2UR per MMA).
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();       // 0 = leader (issues the pair's MMAs), 1 = peer
+  const int64_t pair_id = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const bool want_rgb = dst.rgb != nullptr;
   const int n_layers = want_rgb ? kNumLayers : 8;
   const int64_t n_tiles = (src.B + kTileM - 1) / kTileM;
-  const int64_t n_pairs = (n_tiles + 1) / 2;
+  const int64_t n_quads = (n_tiles + 3) / 4;  // quad u = tiles 4u..4u+3: slot s of CTA r owns tile 4u + 2s + r
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(bar_full + 8 * s, 1);
-      mbar_init(bar_empty + 8 * s, 1);
+      mbar_init(bar_full + 8 * s, 1);   // this CTA's bulk copy (expect_tx)
+      mbar_init(bar_pfull + 8 * s, 2);  // leader only: both CTAs' relays
+      mbar_init(bar_empty + 8 * s, 2);  // slot X's and slot Y's commit
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_acc + 8 * s, 1);
-      mbar_init(bar_act + 8 * s, kEpiThreadsPerSlot);
+      mbar_init(bar_act + 8 * s, 16);   // leader only: one elected arrive per epilogue warp of the slot, both CTAs
     }
     fence_barrier_init();
   }
   if (warp == 2) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(base + kOffBar + 64), "r"(512u)
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(base + kOffBar + kTmemSlotOff),
+                 "r"(512u)
                  : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
+  cluster_sync_all();  // barriers of both CTAs initialised before anyone arrives remotely
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  int n_chunks_quad = 0;
+  for (int l = 0; l < n_layers; ++l) n_chunks_quad += layer_chunks(l);
+
   if (warp == 0) {
-    // ===================================================== TMA producer: stream weight chunks through the ring
-    {
-      Tracer tr{(trace != nullptr && blockIdx.x == 0 && lane == 0) ? trace + 1 * 2 * kTraceCap : nullptr, 0};
-      uint32_t stage = 0, phase = 0;
-      for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
-        const uint8_t* src_ptr = chunks;
-        for (int l = 0; l < n_layers; ++l) {
-          const uint32_t bytes = (uint32_t)layer_n(l) * 128u;
-          for (int c = 0; c < layer_chunks(l); ++c) {
-            tr.rec(0x100 | l);
-            mbar_wait(bar_empty + 8 * stage, phase ^ 1u);
-            tr.rec(0x200 | l);
-            if (elect_one()) {
-              mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
-              tma_bulk_g2s(base + kOffStage + stage * kStageBytes, src_ptr, bytes, bar_full + 8 * stage);
-            }
-            __syncwarp();
-            src_ptr += bytes;
-            if (++stage == kStages) { stage = 0; phase ^= 1u; }
+    // ===================================================== TMA producer: this CTA's half of every weight chunk
+    Tracer tr{(trace != nullptr && blockIdx.x == 0 && lane == 0) ? trace + 1 * 2 * kTraceCap : nullptr, 0};
+    uint32_t stage = 0, phase = 0;
+    for (int64_t quad = pair_id; quad < n_quads; quad += n_pairs) {
+      const uint8_t* src_ptr = chunks;
+      for (int l = 0; l < n_layers; ++l) {
+        const uint32_t bytes = (uint32_t)layer_n(l) * 64u;  // [N/2 x 64] 16-bit
+        for (int c = 0; c < layer_chunks(l); ++c) {
+          tr.rec(0x100 | l);
+          mbar_wait(bar_empty + 8 * stage, phase ^ 1u);
+          tr.rec(0x200 | l);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
+            tma_bulk_g2s(base + kOffStage + stage * kStageBytes, src_ptr + rank * bytes, bytes, bar_full + 8 * stage);
           }
+          __syncwarp();
+          src_ptr += 2 * bytes;
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
       }
     }
+  } else if (warp == 3) {
+    // ===================================================== relay: tell the leader that this CTA's half has landed
+    uint32_t stage = 0, phase = 0;
+    for (int64_t quad = pair_id; quad < n_quads; quad += n_pairs) {
+      for (int c = 0; c < n_chunks_quad; ++c) {
+        mbar_wait(bar_full + 8 * stage, phase);
+        if (elect_one()) mbar_arrive_cluster(bar_pfull + 8 * stage, 0u);
+        __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
+      }
+    }
   } else if (warp == 1) {
-    // ===================================================== MMA issuer: one thread drives the tensor core
-    {
+    // ===================================================== MMA issuer (leader CTA): one thread drives both tensor cores
+    if (rank == 0) {
       Tracer tr{(trace != nullptr && blockIdx.x == 0 && lane == 0) ? trace : nullptr, 0};
-      uint32_t stage = 0, phase = 0, act_par[2] = {0u, 0u};
-      for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
-        const int n_active = (2 * pair + 1 < n_tiles) ? 2 : 1;
-        for (int l = 0; l < n_layers; ++l) {
-          const uint32_t idesc = make_idesc(kFp16 ? 1 : 0, layer_n(l));
+      Stream st[2];
+      for (int s = 0; s < 2; ++s) st[s] = Stream{pair_id, 0, 0, 0u, 0u, pair_id >= n_quads};
+      uint32_t full_seen = 0;  // chunks [0, full_seen) are known to be resident (they land in order)
+      const uint64_t act_desc[2] = {make_desc(base + kOffAct), make_desc(base + kOffAct + kActBytes)};
+      const uint64_t aux_desc[2] = {make_desc(base + kOffAux), make_desc(base + kOffAux + kAuxBytes)};
+      const uint64_t stage_desc0 = make_desc(base + kOffStage);
+      uint32_t idle = 0;
+      while (!(st[0].done && st[1].done)) {
+        bool advanced_x = false;
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          Stream& t = st[s];
+          if (t.done) continue;
+          // slot Y keeps kSkew chunks behind X while X can run: its epilogue then overlaps X's MMAs and vice versa
+          if (s == 1 && !st[0].done && advanced_x && t.g + kSkew > st[0].g) continue;
+          const uint32_t stage = t.g & (kStages - 1);
+          if (t.g >= full_seen) {  // both halves of the chunk landed?
+            if (!mbar_test_cluster(bar_pfull + 8 * stage, (t.g / kStages) & 1u)) continue;
+            full_seen = t.g + 1;
+          }
+          if (t.c == 0) {  // layer start: the slot's input operand written and its accumulator drained (both CTAs)
+            if (!mbar_test_cluster(bar_act + 8 * s, t.act_par)) continue;
+            t.act_par ^= 1u;
+          }
+          tc_fence_after();
+          const int l = t.l, c = t.c;
           const int nch = layer_chunks(l);
-          for (int c = 0; c < nch; ++c) {
-            tr.rec(0x100 | (l << 4) | c);
-            mbar_wait(bar_full + 8 * stage, phase);
-            tr.rec(0x200 | (l << 4) | c);
-            tc_fence_after();
-            const bool bias_chunk = layer_has_bias_chunk(l) && c == 0;
-            const bool from_aux = bias_chunk || (l == 0) || (l == 5 && c == 0) || (l == 9 && c == 4);
-            const int ks0 = bias_chunk ? 3 : 0;             // bias chunk: only the K16 step holding the ones column
-            const int ks1 = (l == 9 && c == 4) ? 2 : 4;     // PE4(dir): 27 rows + ones column, padded to K = 32
-            const int kb = (l == 9) ? c : c - 1;
-            const uint32_t b_addr = base + kOffStage + stage * kStageBytes;
-            for (int s = 0; s < n_active; ++s) {
-              if (c == 0) {  // this slot's input operand (and drained accumulator) for layer l
-                mbar_wait(bar_act + 8 * s, act_par[s]);
-                act_par[s] ^= 1u;
-                tc_fence_after();
-                tr.rec(0x300 | (l << 4) | s);
+          const bool bias_chunk = layer_has_bias_chunk(l) && c == 0;
+          const bool from_aux = bias_chunk || (l == 0) || (l == 5 && c == 0) || (l == 9 && c == 4);
+          const int kb = (l == 9) ? c : c - 1;
+          const uint64_t ad = from_aux ? aux_desc[s] : act_desc[s] + (uint32_t)kb * (kKBlockBytes >> 4);
+          const uint64_t bd = stage_desc0 + stage * (kStageBytes >> 4);
+          const uint32_t d_tmem = tmem_base + (uint32_t)s * 256u;
+          const uint32_t idesc = make_idesc(kFp16 ? 1 : 0, layer_n(l));
+          tr.rec(0x100 | (l << 4) | c | (s << 12));
+          if (elect_one()) {
+            if (bias_chunk) {  // only the K16 step holding the ones column
+              tc_mma2_f16(d_tmem, ad + 6, bd + 6, idesc, 0u);
+            } else {
+              tc_mma2_f16(d_tmem, ad, bd, idesc, c != 0 ? 1u : 0u);
+              tc_mma2_f16(d_tmem, ad + 2, bd + 2, idesc, 1u);
+              if (!(l == 9 && c == 4)) {  // PE4(dir): 27 rows + ones column, padded to K = 32
+                tc_mma2_f16(d_tmem, ad + 4, bd + 4, idesc, 1u);
+                tc_mma2_f16(d_tmem, ad + 6, bd + 6, idesc, 1u);
               }
-              const uint32_t a_addr =
-                  from_aux ? base + kOffAux + s * kAuxBytes : base + kOffAct + s * kActBytes + kb * kKBlockBytes;
-              const uint32_t d_tmem = tmem_base + (uint32_t)s * 256u;
-              // Descriptors are built once per chunk; a K16 step only advances the start-address field (+32 B = +2).
-              const uint64_t ad = make_desc(a_addr), bd = make_desc(b_addr);
-              if (elect_one()) {
-                if (ks0 == 0 && ks1 == 4) {
-                  tc_mma_f16(d_tmem, ad, bd, idesc, c != 0 ? 1u : 0u);
-                  tc_mma_f16(d_tmem, ad + 2, bd + 2, idesc, 1u);
-                  tc_mma_f16(d_tmem, ad + 4, bd + 4, idesc, 1u);
-                  tc_mma_f16(d_tmem, ad + 6, bd + 6, idesc, 1u);
-                } else {
-                  for (int ks = ks0; ks < ks1; ++ks)
-                    tc_mma_f16(d_tmem, ad + 2 * ks, bd + 2 * ks, idesc, (c != 0 || ks != ks0) ? 1u : 0u);
-                }
-                if (c == nch - 1) tc_commit(bar_acc + 8 * s);  // accumulator of this layer complete -> epilogue
-              }
-              __syncwarp();
             }
-            if (elect_one()) tc_commit(bar_empty + 8 * stage);  // both slots consumed the chunk -> refill allowed
-            __syncwarp();
-            if (++stage == kStages) { stage = 0; phase ^= 1u; }
+            if (c == nch - 1) tc_commit2(bar_acc + 8 * s);  // this layer's accumulator complete -> both epilogues
+            tc_commit2(bar_empty + 8 * stage);               // this slot is done with the chunk (both CTAs' rings)
+          }
+          __syncwarp();
+          if (s == 0) advanced_x = true;
+          idle = 0;
+          ++t.g;
+          if (++t.c == nch) {
+            t.c = 0;
+            if (++t.l == n_layers) {
+              t.l = 0;
+              t.quad += n_pairs;
+              t.done = t.quad >= n_quads;
+            }
           }
         }
+        if (++idle > (1u << 22)) __trap();  // protocol bug: trap instead of hanging the GPU
       }
     }
   } else if (warp >= 4) {
@@ -412,9 +514,9 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
     uint32_t acc_par = 0;
     Tracer tr{(trace != nullptr && blockIdx.x == 0 && quad == 0 && lane == 0) ? trace + (2 + slot * 2 + half) * 2 * kTraceCap
                                                                              : nullptr, 0};
-    for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
-      const int64_t tile = 2 * pair + slot;
-      if (tile >= n_tiles) continue;
+    for (int64_t qd = pair_id; qd < n_quads; qd += n_pairs) {
+      // tiles past the end run through the same barrier protocol on zero inputs and store nothing
+      const int64_t tile = 4 * qd + 2 * slot + (int64_t)rank;
       tr.rec(0x500);
       const int64_t g = tile * kTileM + row;
       const bool valid = g < src.B;
@@ -448,7 +550,8 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
       }
       fence_proxy_async();
       tc_fence_before();
-      mbar_arrive(act_bar);
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
       tr.rec(0x400);
 
       float sig = half == 0 ? __ldg(&Cg->b_alpha) : 0.0f;
@@ -459,22 +562,24 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
         acc_par ^= 1u;
         tc_fence_after();
         tr.rec(0x200 | l);
-        epi_layer<kFp16, true, false, true>(taddr, Cg->w_alpha, sig, act_row, r8, cb0);
+        epi_layer<kFp16, true, false, true>(tr, taddr, Cg->w_alpha, sig, act_row, r8, cb0);
         fence_proxy_async();
         tc_fence_before();
-        mbar_arrive(act_bar);
+        __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
         tr.rec(0x300 | l);
       }
       mbar_wait(acc_bar, acc_par);  // dense7 -> h8; sigma = relu(alpha(h8)) (network.rs:216)
       acc_par ^= 1u;
       tc_fence_after();
       if (want_rgb) {
-        epi_layer<kFp16, true, true, true>(taddr, Cg->w_alpha, sig, act_row, r8, cb0);
+        epi_layer<kFp16, true, true, true>(tr, taddr, Cg->w_alpha, sig, act_row, r8, cb0);
         fence_proxy_async();
         tc_fence_before();
-        mbar_arrive(act_bar);
+        __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
       } else {
-        epi_layer<kFp16, true, true, false>(taddr, Cg->w_alpha, sig, act_row, r8, cb0);
+        epi_layer<kFp16, true, true, false>(tr, taddr, Cg->w_alpha, sig, act_row, r8, cb0);
         tc_fence_before();
       }
       if (half == 1) scratch[0] = sig;
@@ -485,7 +590,7 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
         mbar_wait(acc_bar, acc_par);  // bottleneck, ActivationType::None (network.rs:218)
         acc_par ^= 1u;
         tc_fence_after();
-        epi_layer<kFp16, false, false, true>(taddr, Cg->w_alpha, sig, act_row, r8, cb0);
+        epi_layer<kFp16, false, false, true>(tr, taddr, Cg->w_alpha, sig, act_row, r8, cb0);
         // PE4(dir) replaces PE10(p) in the aux tile: the skip MMA that read it finished layers ago
         if (half == 0) {
           write_raw3<kFp16>(aux, row, d);
@@ -497,7 +602,8 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
         }
         fence_proxy_async();
         tc_fence_before();
-        mbar_arrive(act_bar);
+        __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
 
         mbar_wait(acc_bar, acc_par);  // viewdirs (ReLU) then the f32 rgb head + sigmoid (network.rs:222-223)
         acc_par ^= 1u;
@@ -541,8 +647,9 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
 
   tc_fence_before();
   __syncthreads();
+  cluster_sync_all();  // the peer's shared memory and TMEM stay alive until the pair's last MMA has been consumed
   if (warp == 2) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
   }
 }
 
@@ -634,8 +741,9 @@ cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const Sample
                           cudaStream_t s) {
   if (src.B == 0) return cudaSuccess;
   const int64_t n_tiles = (src.B + kTileM - 1) / kTileM;
-  const int64_t n_pairs = (n_tiles + 1) / 2;
-  const int grid = (int)(n_pairs < sm_count ? n_pairs : sm_count);
+  const int64_t n_quads = (n_tiles + 3) / 4;  // a CTA pair works on four tiles at a time
+  const int64_t max_pairs = sm_count / 2;
+  const int grid = 2 * (int)(n_quads < max_pairs ? n_quads : max_pairs);
   cudaError_t e;
   unsigned long long* trace = nullptr;
   const char* trace_path = std::getenv("NERF_B200_TRACE");  // developer timeline, off in production
