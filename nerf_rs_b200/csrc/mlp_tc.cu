@@ -8,11 +8,14 @@
 //     and writes the next layer's A operand straight into its own CTA's shared memory in the K-major
 //     SWIZZLE_128B layout the MMA descriptor expects.
 //   - B (weights) is split by N between the two CTAs: each CTA streams only its [N/2 x 64] half of every chunk
-//     (16 KiB) from L2 with 1-D bulk TMA copies, so the 64 KiB ring is four chunks deep (it was two with
-//     cta_group::1) and L2 -> SMEM traffic per SM is halved again.  Both slots consume a chunk before it is released.
-//   - The four-deep ring is what lets the two slots run out of step: the leader's MMA thread advances slot X and slot
-//     Y independently (Y at least two chunks behind X while X can run), so one slot's epilogue overlaps the other
-//     slot's MMAs instead of idling the tensor pipe at every layer boundary.
+//     (16 KiB) from L2 with 1-D bulk TMA copies into a four-deep ring.  Both slots consume a chunk before it is
+//     released, so L2 -> SMEM traffic is one weight pass per four tiles.
+//   - Bias never goes through the tensor core: after an epilogue thread has read a block of accumulator columns it
+//     writes the NEXT layer's bias (exact f32) back into them with tcgen05.st, and every MMA accumulates.
+//   - The issue order is static: slot X's layer l, then slot Y's layer l, then X's layer l + 1, ...  The single
+//     MMA thread blocks on one barrier at a time and runs ahead of the tensor pipe, so while slot X's epilogue
+//     drains layer l the pipe is busy with Y's layer l (already queued) and vice versa.  A 256-wide layer is four
+//     chunks = the whole ring; the only five-chunk layer (dense5) is issued X0-3, Y0-2, X4, Y3-4.
 //   - concat_rows(h0, h4) (network.rs:210) is split-K: the PE tile (K = 64) and h4 (K = 256) accumulate into
 //     the same D.  concat_rows(bottleneck, PE4(dir)) (network.rs:220) likewise (K = 256 + 32).
 //   - sigma (256 -> 1) and rgb (128 -> 3) heads are f32 dot products in the epilogue on the f32 accumulators.
@@ -46,18 +49,17 @@ constexpr uint32_t kOffAct = 0;
 constexpr uint32_t kOffAux = kOffAct + 2 * kActBytes;
 constexpr uint32_t kOffStage = kOffAux + 2 * kAuxBytes;
 constexpr uint32_t kOffBar = kOffStage + kStages * kStageBytes;
-// barrier block, 8 B each: full[4] pfull[4] empty[4] acc[2] act[2]
+// barrier block, 8 B each: full[4] pfull[4] empty[4] acc[2] act[2] | tmem slot
 constexpr uint32_t kBarFull = 0, kBarPFull = 32, kBarEmpty = 64, kBarAcc = 96, kBarAct = 112, kTmemSlotOff = 128;
-constexpr uint32_t kSmemBytes = kOffBar + 256 + 1024;  // + barriers + slack for manual 1 KiB alignment
-constexpr int kSkew = 2;  // slot Y trails slot X by at least this many chunks while X can advance
+constexpr uint32_t kSmemBytes = kOffBar + 256;  // 224.25 KiB
+static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
+constexpr int kLead = 4;  // chunks of a layer slot X issues before slot Y starts the same layer
 
 // Layer table: chunks per layer in consumption order.
 constexpr int kNumLayers = 10;  // dense0..7, bottleneck, viewdirs
-// Bias rides on the tensor core: the aux tile carries a constant-1 column (k = 63 of PE10(p), k = 31 of PE4(dir))
-// and the matching weight row holds the layer's bias.  dense0 / dense5 / viewdirs have a PE chunk anyway; every
-// other layer starts with a "bias chunk" (only row k = 63 non-zero) of which a single K16 step is issued.
-__host__ __device__ constexpr int layer_chunks(int l) { return l == 0 ? 1 : 5; }
-__host__ __device__ constexpr bool layer_has_bias_chunk(int l) { return l != 0 && l != 5 && l != 9; }
+// A ring chunk is one [N/2 x 64] weight half per CTA (16 KiB at N = 256, 8 KiB for viewdirs).  dense0 is the PE
+// chunk alone, dense5 the PE chunk + four K-blocks of h4, viewdirs four K-blocks of the bottleneck + the PE4(dir) chunk.
+__host__ __device__ constexpr int layer_chunks(int l) { return l == 0 ? 1 : ((l == 5 || l == 9) ? 5 : 4); }
 __host__ __device__ constexpr int layer_n(int l) { return l == 9 ? 128 : 256; }
 
 // ------------------------------------------------------------------------------------------ PTX wrappers
@@ -257,20 +259,20 @@ struct Tracer {
 // A 256-wide layer is drained by 8 warps per tile slot: warp (quad, half) owns TMEM lanes 32*quad..+31
 // (one sample row per thread) and columns 128*half..+127, as four 32-column blocks.  TMEM loads are software
 // pipelined: block b+1 is in flight while block b is converted and stored.
-// One 32-column block of the accumulator (bias already inside, see layer_has_bias_chunk): optional sigma
-// partial on the unrounded f32 values; optional ReLU + 16-bit store into the next layer's A tile.
-template <bool kFp16, bool kRelu, bool kSigma, bool kStore>
-__device__ __forceinline__ void epi_block(const uint32_t (&v)[32], const float* __restrict__ walpha, float& sig,
-                                          uint8_t* act_row, uint32_t r8, int cb) {
+// One 32-column block of the accumulator: optional f32 bias (layers without a PE chunk; the others carry it through
+// the ones column), optional sigma partial on the unrounded f32 values; optional ReLU + 16-bit store into the next
+// layer's A tile.  `bias` and `walpha` point into the kernel's constant bank (warp-uniform operands).
+template <bool kFp16, bool kRelu, bool kSigma, bool kStore, bool kBias>
+__device__ __forceinline__ void epi_block(uint32_t (&v)[32], const float* __restrict__ bias,
+                                          const float* __restrict__ walpha, float& sig, uint8_t* act_row, uint32_t r8,
+                                          int cb) {
+  if constexpr (kBias) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + bias[cb * 32 + j]);
+  }
   if constexpr (kSigma) {
 #pragma unroll
-    for (int j = 0; j < 32; j += 4) {
-      const float4 w = __ldg(reinterpret_cast<const float4*>(walpha + cb * 32 + j));
-      sig = fmaf(fmaxf(__uint_as_float(v[j]), 0.0f), w.x, sig);
-      sig = fmaf(fmaxf(__uint_as_float(v[j + 1]), 0.0f), w.y, sig);
-      sig = fmaf(fmaxf(__uint_as_float(v[j + 2]), 0.0f), w.z, sig);
-      sig = fmaf(fmaxf(__uint_as_float(v[j + 3]), 0.0f), w.w, sig);
-    }
+    for (int j = 0; j < 32; ++j) sig = fmaf(fmaxf(__uint_as_float(v[j]), 0.0f), walpha[cb * 32 + j], sig);
   }
   if constexpr (kStore) {
     uint8_t* kblock = act_row + (cb >> 1) * kKBlockBytes;
@@ -288,22 +290,24 @@ __device__ __forceinline__ void epi_block(const uint32_t (&v)[32], const float* 
 }
 
 // Four 32-column blocks starting at block cb0, TMEM loads double-buffered.
-template <bool kFp16, bool kRelu, bool kSigma, bool kStore>
-__device__ __forceinline__ void epi_layer(Tracer& tr, uint32_t taddr, const float* __restrict__ walpha, float& sig,
-                                          uint8_t* act_row, uint32_t r8, int cb0) {
+template <bool kFp16, bool kRelu, bool kSigma, bool kStore, bool kBias>
+__device__ __forceinline__ void epi_layer(Tracer& tr, uint32_t taddr, const float* __restrict__ bias,
+                                          const float* __restrict__ walpha, float& sig, uint8_t* act_row, uint32_t r8,
+                                          int cb0) {
   uint32_t va[32], vb[32];
-  tc_ld32(taddr + cb0 * 32, va);
-  tc_ld32(taddr + (cb0 + 1) * 32, vb);
+  const uint32_t t0 = taddr + cb0 * 32;
+  tc_ld32(t0, va);
+  tc_ld32(t0 + 32, vb);
   tc_wait_ld();
   tr.rec(0x600);
-  epi_block<kFp16, kRelu, kSigma, kStore>(va, walpha, sig, act_row, r8, cb0);
-  tc_ld32(taddr + (cb0 + 2) * 32, va);
-  epi_block<kFp16, kRelu, kSigma, kStore>(vb, walpha, sig, act_row, r8, cb0 + 1);
-  tc_ld32(taddr + (cb0 + 3) * 32, vb);
+  epi_block<kFp16, kRelu, kSigma, kStore, kBias>(va, bias, walpha, sig, act_row, r8, cb0);
+  tc_ld32(t0 + 64, va);
+  epi_block<kFp16, kRelu, kSigma, kStore, kBias>(vb, bias, walpha, sig, act_row, r8, cb0 + 1);
+  tc_ld32(t0 + 96, vb);
   tc_wait_ld();
   tr.rec(0x700);
-  epi_block<kFp16, kRelu, kSigma, kStore>(va, walpha, sig, act_row, r8, cb0 + 2);
-  epi_block<kFp16, kRelu, kSigma, kStore>(vb, walpha, sig, act_row, r8, cb0 + 3);
+  epi_block<kFp16, kRelu, kSigma, kStore, kBias>(va, bias, walpha, sig, act_row, r8, cb0 + 2);
+  epi_block<kFp16, kRelu, kSigma, kStore, kBias>(vb, bias, walpha, sig, act_row, r8, cb0 + 3);
 }
 
 // positional_encoding_* (network.rs:263-330): octaves [o0, o1) of one sample into row `row` of an aux tile.
@@ -332,24 +336,14 @@ __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t threads) {
 
 
 // ------------------------------------------------------------------------------------------ the kernel
-// Position of a slot's MMA stream: chunk c of layer l of the pair's q-th quad; g counts chunks since kernel start
-// (ring stage = g % kStages, ring phase = (g / kStages) & 1).
-struct Stream {
-  int64_t quad;
-  int l, c;
-  uint32_t g;
-  uint32_t act_par;
-  bool done;
-};
-
 template <bool kFp16>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
-mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunks, const SampleSrc src,
+mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ chunks, const SampleSrc src,
               const SampleDst dst, unsigned long long* __restrict__ trace) {
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t raw = smem_u32(smem_raw);
-  const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B atoms need 1 KiB alignment
-  uint8_t* smem = smem_raw + (base - raw);
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  const uint32_t base = smem_u32(smem_raw);
+  if ((base & 1023u) != 0u) __trap();  // SWIZZLE_128B atoms need 1 KiB alignment; the kernel has no static shared memory
   const uint32_t bar0 = base + kOffBar;
   const uint32_t bar_full = bar0 + kBarFull, bar_pfull = bar0 + kBarPFull, bar_empty = bar0 + kBarEmpty,
                  bar_acc = bar0 + kBarAcc, bar_act = bar0 + kBarAct;
@@ -416,12 +410,18 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
     }
   } else if (warp == 3) {
     // ===================================================== relay: tell the leader that this CTA's half has landed
+    Tracer tr{(trace != nullptr && blockIdx.x == 0 && lane == 0) ? trace + 6 * 2 * kTraceCap : nullptr, 0};
     uint32_t stage = 0, phase = 0;
     for (int64_t quad = pair_id; quad < n_quads; quad += n_pairs) {
       for (int c = 0; c < n_chunks_quad; ++c) {
         mbar_wait(bar_full + 8 * stage, phase);
+        tr.rec(0x300 | stage);
         if (elect_one()) mbar_arrive_cluster(bar_pfull + 8 * stage, 0u);
         __syncwarp();
+        if (tr.p != nullptr) {  // timeline only: when did the peer's half land too
+          mbar_wait(bar_pfull + 8 * stage, phase);
+          tr.rec(0x400 | stage);
+        }
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
@@ -429,69 +429,61 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
     // ===================================================== MMA issuer (leader CTA): one thread drives both tensor cores
     if (rank == 0) {
       Tracer tr{(trace != nullptr && blockIdx.x == 0 && lane == 0) ? trace : nullptr, 0};
-      Stream st[2];
-      for (int s = 0; s < 2; ++s) st[s] = Stream{pair_id, 0, 0, 0u, 0u, pair_id >= n_quads};
-      uint32_t full_seen = 0;  // chunks [0, full_seen) are known to be resident (they land in order)
-      const uint64_t act_desc[2] = {make_desc(base + kOffAct), make_desc(base + kOffAct + kActBytes)};
-      const uint64_t aux_desc[2] = {make_desc(base + kOffAux), make_desc(base + kOffAux + kAuxBytes)};
+      const uint64_t act_desc0 = make_desc(base + kOffAct), aux_desc0 = make_desc(base + kOffAux);
       const uint64_t stage_desc0 = make_desc(base + kOffStage);
-      uint32_t idle = 0;
-      while (!(st[0].done && st[1].done)) {
-        bool advanced_x = false;
-#pragma unroll
-        for (int s = 0; s < 2; ++s) {
-          Stream& t = st[s];
-          if (t.done) continue;
-          // slot Y keeps kSkew chunks behind X while X can run: its epilogue then overlaps X's MMAs and vice versa
-          if (s == 1 && !st[0].done && advanced_x && t.g + kSkew > st[0].g) continue;
-          const uint32_t stage = t.g & (kStages - 1);
-          if (t.g >= full_seen) {  // both halves of the chunk landed?
-            if (!mbar_test_cluster(bar_pfull + 8 * stage, (t.g / kStages) & 1u)) continue;
-            full_seen = t.g + 1;
-          }
-          if (t.c == 0) {  // layer start: the slot's input operand written and its accumulator drained (both CTAs)
-            if (!mbar_test_cluster(bar_act + 8 * s, t.act_par)) continue;
-            t.act_par ^= 1u;
-          }
-          tc_fence_after();
-          const int l = t.l, c = t.c;
+      uint32_t g0 = 0;       // ring index of the current layer's first chunk (the same for both slots)
+      uint32_t act_par = 0;  // bit s: parity of slot s's "layer input ready" barrier
+      for (int64_t quad = pair_id; quad < n_quads; quad += n_pairs) {
+#pragma unroll 1
+        for (int l = 0; l < n_layers; ++l) {
           const int nch = layer_chunks(l);
-          const bool bias_chunk = layer_has_bias_chunk(l) && c == 0;
-          const bool from_aux = bias_chunk || (l == 0) || (l == 5 && c == 0) || (l == 9 && c == 4);
-          const int kb = (l == 9) ? c : c - 1;
-          const uint64_t ad = from_aux ? aux_desc[s] : act_desc[s] + (uint32_t)kb * (kKBlockBytes >> 4);
-          const uint64_t bd = stage_desc0 + stage * (kStageBytes >> 4);
-          const uint32_t d_tmem = tmem_base + (uint32_t)s * 256u;
           const uint32_t idesc = make_idesc(kFp16 ? 1 : 0, layer_n(l));
-          tr.rec(0x100 | (l << 4) | c | (s << 12));
-          if (elect_one()) {
-            if (bias_chunk) {  // only the K16 step holding the ones column
-              tc_mma2_f16(d_tmem, ad + 6, bd + 6, idesc, 0u);
-            } else {
-              tc_mma2_f16(d_tmem, ad, bd, idesc, c != 0 ? 1u : 0u);
-              tc_mma2_f16(d_tmem, ad + 2, bd + 2, idesc, 1u);
-              if (!(l == 9 && c == 4)) {  // PE4(dir): 27 rows + ones column, padded to K = 32
-                tc_mma2_f16(d_tmem, ad + 4, bd + 4, idesc, 1u);
-                tc_mma2_f16(d_tmem, ad + 6, bd + 6, idesc, 1u);
+          // the chunk that reads the aux tile (PE10(p) for dense0 / dense5, PE4(dir) last for viewdirs); the others
+          // read K-block c - kb_off of the activations
+          const int aux_c = (l == 0 || l == 5) ? 0 : (l == 9 ? 4 : -1);
+          const int kb_off = (l == 5) ? 1 : 0;
+          // Static interleave (X leads Y by kLead chunks): X[0, kLead), Y[0, nch - kLead), X[kLead, nch), Y[rest]:
+          // a stage is released early enough for the next layer's load to land, and each slot's epilogue is covered
+          // by the other slot's queued MMAs.
+          const int nseg = (nch > kLead) ? 4 : 2;
+#pragma unroll 1
+          for (int seg = 0; seg < nseg; ++seg) {
+            const int s = seg & 1;
+            int cb = 0, ce = nch;
+            if (nseg == 4) {
+              const int split = s ? nch - kLead : kLead;
+              if (seg < 2) ce = split; else cb = split;
+            }
+            const uint32_t d_tmem = tmem_base + (uint32_t)s * 256u;
+            const uint64_t auxd = aux_desc0 + (uint32_t)s * (kAuxBytes >> 4);
+            const uint64_t actd = act_desc0 + (uint32_t)s * (kActBytes >> 4) - (uint32_t)kb_off * (kKBlockBytes >> 4);
+#pragma unroll 1
+            for (int c = cb; c < ce; ++c) {
+              const uint32_t g = g0 + (uint32_t)c, stage = g & (kStages - 1);
+              if (c == 0) {  // layer input written and accumulator drained (both CTAs)
+                mbar_wait(bar_act + 8 * s, (act_par >> s) & 1u);
+                act_par ^= 1u << s;
               }
+              if (s == 0) mbar_wait(bar_pfull + 8 * stage, (g / kStages) & 1u);  // X is every chunk's first consumer
+              tc_fence_after();
+              tr.rec(0x100 | (l << 4) | c | (s << 12));
+              const uint64_t bd = stage_desc0 + stage * (kStageBytes >> 4);
+              const uint64_t ad = (c == aux_c) ? auxd : actd + (uint32_t)c * (kKBlockBytes >> 4);
+              if (elect_one()) {
+                tc_mma2_f16(d_tmem, ad, bd, idesc, c != 0 ? 1u : 0u);
+                tc_mma2_f16(d_tmem, ad + 2, bd + 2, idesc, 1u);
+                if (!(l == 9 && c == 4)) {  // PE4(dir) is K = 32: aux columns 32..63 hold f32 scratch by then
+                  tc_mma2_f16(d_tmem, ad + 4, bd + 4, idesc, 1u);
+                  tc_mma2_f16(d_tmem, ad + 6, bd + 6, idesc, 1u);
+                }
+                if (c == nch - 1) tc_commit2(bar_acc + 8 * s);  // this layer's accumulator complete -> both epilogues
+                tc_commit2(bar_empty + 8 * stage);               // this slot is done with the chunk (both CTAs' rings)
+              }
+              __syncwarp();
             }
-            if (c == nch - 1) tc_commit2(bar_acc + 8 * s);  // this layer's accumulator complete -> both epilogues
-            tc_commit2(bar_empty + 8 * stage);               // this slot is done with the chunk (both CTAs' rings)
           }
-          __syncwarp();
-          if (s == 0) advanced_x = true;
-          idle = 0;
-          ++t.g;
-          if (++t.c == nch) {
-            t.c = 0;
-            if (++t.l == n_layers) {
-              t.l = 0;
-              t.quad += n_pairs;
-              t.done = t.quad >= n_quads;
-            }
-          }
+          g0 += (uint32_t)nch;
         }
-        if (++idle > (1u << 22)) __trap();  // protocol bug: trap instead of hanging the GPU
       }
     }
   } else if (warp >= 4) {
@@ -546,7 +538,7 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
         write_octaves<kFp16>(aux, row, p, 0, 5);
       } else {
         write_octaves<kFp16>(aux, row, p, 5, 10);
-        *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, 63)) = cvt1<kFp16>(1.0f);  // ones column: bias row
+        *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, 63)) = 0;  // K padding (weight row 63 is zero too)
       }
       fence_proxy_async();
       tc_fence_before();
@@ -554,7 +546,7 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
       if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
       tr.rec(0x400);
 
-      float sig = half == 0 ? __ldg(&Cg->b_alpha) : 0.0f;
+      float sig = half == 0 ? C.b_alpha : 0.0f;
 #pragma unroll 1
       for (int l = 0; l < 7; ++l) {
         tr.rec(0x100 | l);
@@ -562,24 +554,24 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
         acc_par ^= 1u;
         tc_fence_after();
         tr.rec(0x200 | l);
-        epi_layer<kFp16, true, false, true>(tr, taddr, Cg->w_alpha, sig, act_row, r8, cb0);
+        epi_layer<kFp16, true, false, true, true>(tr, taddr, C.bias[l], C.w_alpha, sig, act_row, r8, cb0);
         fence_proxy_async();
         tc_fence_before();
         __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
+        if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
         tr.rec(0x300 | l);
       }
       mbar_wait(acc_bar, acc_par);  // dense7 -> h8; sigma = relu(alpha(h8)) (network.rs:216)
       acc_par ^= 1u;
       tc_fence_after();
       if (want_rgb) {
-        epi_layer<kFp16, true, true, true>(tr, taddr, Cg->w_alpha, sig, act_row, r8, cb0);
+        epi_layer<kFp16, true, true, true, true>(tr, taddr, C.bias[7], C.w_alpha, sig, act_row, r8, cb0);
         fence_proxy_async();
         tc_fence_before();
         __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
+        if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
       } else {
-        epi_layer<kFp16, true, true, false>(tr, taddr, Cg->w_alpha, sig, act_row, r8, cb0);
+        epi_layer<kFp16, true, true, false, true>(tr, taddr, C.bias[7], C.w_alpha, sig, act_row, r8, cb0);
         tc_fence_before();
       }
       if (half == 1) scratch[0] = sig;
@@ -590,42 +582,37 @@ mlp_tc_kernel(const TcConsts* __restrict__ Cg, const uint8_t* __restrict__ chunk
         mbar_wait(acc_bar, acc_par);  // bottleneck, ActivationType::None (network.rs:218)
         acc_par ^= 1u;
         tc_fence_after();
-        epi_layer<kFp16, false, false, true>(tr, taddr, Cg->w_alpha, sig, act_row, r8, cb0);
+        epi_layer<kFp16, false, false, true, true>(tr, taddr, C.bias[8], C.w_alpha, sig, act_row, r8, cb0);
         // PE4(dir) replaces PE10(p) in the aux tile: the skip MMA that read it finished layers ago
         if (half == 0) {
           write_raw3<kFp16>(aux, row, d);
           write_octaves<kFp16>(aux, row, d, 0, 2);
         } else {
           write_octaves<kFp16>(aux, row, d, 2, 4);
-          for (int k = kDirEnc; k < 31; ++k) *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, k)) = 0;
-          *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, 31)) = cvt1<kFp16>(1.0f);  // ones column: bias row
+          for (int k = kDirEnc; k < 32; ++k) *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, k)) = 0;  // K padding to 32
         }
         fence_proxy_async();
         tc_fence_before();
         __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
+        if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
 
         mbar_wait(acc_bar, acc_par);  // viewdirs (ReLU) then the f32 rgb head + sigmoid (network.rs:222-223)
         acc_par ^= 1u;
         tc_fence_after();
         float r0 = 0.f, r1 = 0.f, r2 = 0.f;
-        if (half == 0) { r0 = __ldg(&Cg->b_rgb[0]); r1 = __ldg(&Cg->b_rgb[1]); r2 = __ldg(&Cg->b_rgb[2]); }
+        if (half == 0) { r0 = C.b_rgb[0]; r1 = C.b_rgb[1]; r2 = C.b_rgb[2]; }
 #pragma unroll 1
         for (int cb = half * 2; cb < half * 2 + 2; ++cb) {
           uint32_t v[32];
           tc_ld32(taddr + cb * 32, v);
           tc_wait_ld();
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 wa = __ldg(reinterpret_cast<const float4*>(&Cg->w_rgb[(cb * 32 + j) * 3]));
-            const float4 wb = __ldg(reinterpret_cast<const float4*>(&Cg->w_rgb[(cb * 32 + j) * 3 + 4]));
-            const float4 wc = __ldg(reinterpret_cast<const float4*>(&Cg->w_rgb[(cb * 32 + j) * 3 + 8]));
-            const float c0 = fmaxf(__uint_as_float(v[j]), 0.0f), c1 = fmaxf(__uint_as_float(v[j + 1]), 0.0f);
-            const float c2 = fmaxf(__uint_as_float(v[j + 2]), 0.0f), c3 = fmaxf(__uint_as_float(v[j + 3]), 0.0f);
-            r0 = fmaf(c0, wa.x, r0); r1 = fmaf(c0, wa.y, r1); r2 = fmaf(c0, wa.z, r2);
-            r0 = fmaf(c1, wa.w, r0); r1 = fmaf(c1, wb.x, r1); r2 = fmaf(c1, wb.y, r2);
-            r0 = fmaf(c2, wb.z, r0); r1 = fmaf(c2, wb.w, r1); r2 = fmaf(c2, wc.x, r2);
-            r0 = fmaf(c3, wc.y, r0); r1 = fmaf(c3, wc.z, r1); r2 = fmaf(c3, wc.w, r2);
+          for (int j = 0; j < 32; ++j) {
+            const int k = cb * 32 + j;
+            const float c = fmaxf(__uint_as_float(v[j]) + C.bias[9][k], 0.0f);
+            r0 = fmaf(c, C.w_rgb[k * 3 + 0], r0);
+            r1 = fmaf(c, C.w_rgb[k * 3 + 1], r1);
+            r2 = fmaf(c, C.w_rgb[k * 3 + 2], r2);
           }
         }
         tc_fence_before();
@@ -666,20 +653,15 @@ inline uint16_t host_cvt(float v, int fmt) {
 }
 
 // Appends the [n x 64] SWIZZLE_128B image of W rows [k0, k0 + krows) (W is [in][out] row-major, so the B
-// operand element (n, k) is W[k0 + k][n]); rows beyond krows are zero padding, except row `bias_k` (if >= 0),
-// which holds the layer's bias and meets the ones column of the aux tile.
-void append_chunk(std::vector<uint8_t>& img, const std::vector<float>* W, int out_dim, int k0, int krows, int n,
-                  int fmt, const std::vector<float>* bias, int bias_k) {
+// operand element (n, k) is W[k0 + k][n]); rows beyond krows are zero padding.
+void append_chunk(std::vector<uint8_t>& img, const std::vector<float>& W, int out_dim, int k0, int krows, int n,
+                  int fmt) {
   const size_t base = img.size();
   img.resize(base + (size_t)n * 128, 0);
   for (int row = 0; row < n; ++row) {
     for (int k = 0; k < krows; ++k) {
-      const uint16_t h = host_cvt((*W)[(size_t)(k0 + k) * out_dim + row], fmt);
+      const uint16_t h = host_cvt(W[(size_t)(k0 + k) * out_dim + row], fmt);
       std::memcpy(&img[base + sw128_offset((uint32_t)row, (uint32_t)k)], &h, 2);
-    }
-    if (bias != nullptr) {
-      const uint16_t h = host_cvt((*bias)[row], fmt);
-      std::memcpy(&img[base + sw128_offset((uint32_t)row, (uint32_t)bias_k)], &h, 2);
     }
   }
 }
@@ -697,17 +679,17 @@ int build_tc_weights(const TensorMap& t, int fmt, const NetF32&, TcWeights* out)
     const std::vector<float>& b = t.at(std::string(names[l]) + "_bias").data;
     const int n = layer_n(l);
     for (int o = 0; o < n; ++o) out->consts.bias[l][o] = b[o];
+    // K-block images in consumption order; the bias stays f32 (consts.bias) and is added in the epilogue
     if (l == 0) {
-      append_chunk(img, &W, n, 0, kPosEnc, n, fmt, &b, 63);  // PE10 rows 0..62, bias at k = 63
+      append_chunk(img, W, n, 0, kPosEnc, n, fmt);  // PE10 rows 0..62
     } else if (l == 5) {
-      append_chunk(img, &W, n, 0, kPosEnc, n, fmt, &b, 63);  // rows 0..62 multiply h0 (concat_rows(h0, h4), network.rs:210)
-      for (int c = 0; c < 4; ++c) append_chunk(img, &W, n, kPosEnc + 64 * c, 64, n, fmt, nullptr, 0);
+      append_chunk(img, W, n, 0, kPosEnc, n, fmt);  // rows 0..62 multiply h0 (concat_rows(h0, h4), network.rs:210)
+      for (int c = 0; c < 4; ++c) append_chunk(img, W, n, kPosEnc + 64 * c, 64, n, fmt);
     } else if (l == 9) {
-      for (int c = 0; c < 4; ++c) append_chunk(img, &W, n, 64 * c, 64, n, fmt, nullptr, 0);  // bottleneck FIRST (network.rs:220)
-      append_chunk(img, &W, n, kHidden, kDirEnc, n, fmt, &b, 31);  // then PE4(dir) rows 256..282, bias at k = 31
+      for (int c = 0; c < 4; ++c) append_chunk(img, W, n, 64 * c, 64, n, fmt);  // bottleneck FIRST (network.rs:220)
+      append_chunk(img, W, n, kHidden, kDirEnc, n, fmt);                        // then PE4(dir) rows 256..282
     } else {
-      append_chunk(img, nullptr, n, 0, 0, n, fmt, &b, 63);  // bias chunk
-      for (int c = 0; c < 4; ++c) append_chunk(img, &W, n, 64 * c, 64, n, fmt, nullptr, 0);
+      for (int c = 0; c < 4; ++c) append_chunk(img, W, n, 64 * c, 64, n, fmt);
     }
   }
   const std::vector<float>& wa = t.at("alpha_kernel").data;
@@ -720,8 +702,6 @@ int build_tc_weights(const TensorMap& t, int fmt, const NetF32&, TcWeights* out)
   out->bytes = img.size();
   cudaError_t e = cudaMalloc(&out->d_chunks, img.size());
   if (e == cudaSuccess) e = cudaMemcpy(out->d_chunks, img.data(), img.size(), cudaMemcpyHostToDevice);
-  if (e == cudaSuccess) e = cudaMalloc(&out->d_consts, sizeof(TcConsts));
-  if (e == cudaSuccess) e = cudaMemcpy(out->d_consts, &out->consts, sizeof(TcConsts), cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
     set_error(std::string("upload tensor-core weight tiles: ") + cudaGetErrorString(e));
     return NERF_E_CUDA;
@@ -731,9 +711,7 @@ int build_tc_weights(const TensorMap& t, int fmt, const NetF32&, TcWeights* out)
 
 void free_tc_weights(TcWeights* w) {
   if (w->d_chunks) cudaFree(w->d_chunks);
-  if (w->d_consts) cudaFree(w->d_consts);
   w->d_chunks = nullptr;
-  w->d_consts = nullptr;
   w->bytes = 0;
 }
 
@@ -747,7 +725,7 @@ cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const Sample
   cudaError_t e;
   unsigned long long* trace = nullptr;
   const char* trace_path = std::getenv("NERF_B200_TRACE");  // developer timeline, off in production
-  const size_t trace_bytes = 6 * 2 * kTraceCap * sizeof(unsigned long long);
+  const size_t trace_bytes = 7 * 2 * kTraceCap * sizeof(unsigned long long);
   if (trace_path != nullptr) {
     if ((e = cudaMalloc(&trace, trace_bytes)) != cudaSuccess) return e;
     cudaMemsetAsync(trace, 0, trace_bytes, s);
@@ -755,11 +733,11 @@ cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const Sample
   if (w.fmt == 1) {
     e = cudaFuncSetAttribute(mlp_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e != cudaSuccess) return e;
-    mlp_tc_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(w.d_consts, w.d_chunks, src, dst, trace);
+    mlp_tc_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace);
   } else {
     e = cudaFuncSetAttribute(mlp_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e != cudaSuccess) return e;
-    mlp_tc_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(w.d_consts, w.d_chunks, src, dst, trace);
+    mlp_tc_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace);
   }
   e = cudaGetLastError();
   if (trace != nullptr) {

@@ -5,8 +5,8 @@
 
 namespace nerf {
 
-// Small f32 tables the epilogue needs; they live in global memory and are read with warp-uniform 16-byte
-// loads (L1 hits), which is cheaper than register-indexed constant-bank loads.
+// Small f32 tables the epilogue needs.  The struct is a __grid_constant__ kernel parameter (12.5 KiB), so every
+// entry is a warp-uniform constant-bank operand: no loads, no shared memory.
 struct alignas(16) TcConsts {
   float bias[10][256];   // dense0..7, bottleneck, viewdirs (128 used)
   float w_alpha[256];    // sigma head weights (network.rs:216), evaluated in f32 in the epilogue
@@ -20,7 +20,6 @@ struct alignas(16) TcConsts {
 // (N=256: 32 KiB; viewdirs N=128: 16 KiB), so the kernel streams it with a 1-D bulk TMA copy.
 struct TcWeights {
   uint8_t* d_chunks = nullptr;
-  TcConsts* d_consts = nullptr;
   size_t bytes = 0;
   int fmt = 0;  // 0 = bf16, 1 = fp16
   TcConsts consts;

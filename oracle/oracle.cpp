@@ -78,18 +78,16 @@ struct Layer {
   int in = 0, out = 0;
   std::vector<float> w;  // [in][out] row-major, exactly the .bin contents (network.rs:63, lib.rs:121)
   std::vector<float> b;  // [out]
-  mutable std::vector<float> w_rounded[4], b_rounded[4];  // built by prepare() before any parallel region
+  mutable std::vector<float> w_rounded[4];  // built by prepare() before any parallel region
   void prepare(int mode) const {
     if (mode == ORACLE_ROUND_NONE || !w_rounded[mode].empty()) return;
-    std::vector<float> tmp(w.size()), tb(b.size());
+    std::vector<float> tmp(w.size());
     for (size_t i = 0; i < w.size(); ++i) tmp[i] = round_mode_apply(w[i], mode);
-    for (size_t i = 0; i < b.size(); ++i) tb[i] = round_mode_apply(b[i], mode);
     w_rounded[mode].swap(tmp);
-    b_rounded[mode].swap(tb);
   }
   const float* weights(int mode) const { return mode == ORACLE_ROUND_NONE ? w.data() : w_rounded[mode].data(); }
-  // The tensor-core kernel feeds the bias through the MMA (a ones column), so it is an operand too.
-  const float* bias(int mode) const { return mode == ORACLE_ROUND_NONE ? b.data() : b_rounded[mode].data(); }
+  // The tensor-core kernel preloads the f32 accumulator with the bias, so the bias is never rounded.
+  const float* bias(int) const { return b.data(); }
 };
 
 enum Act { RELU, SIGMOID, NONE };  // network.rs:67-72

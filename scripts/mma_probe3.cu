@@ -79,12 +79,12 @@ __host__ __device__ inline float a_val(int m, int k) { return (float)((m * 7 + k
 __host__ __device__ inline float b_val(int n, int k) { return (float)((n * 5 + k) % 13 - 6) * 0.25f; }
 
 // D[256 x 256] = A[256 x 64] * B[256 x 64]^T; CTA r holds A rows 128r.. and B rows (N) 128r..
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(160, 1) probe(float* out, long long* cyc, int timing_mmas) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(160, 1) probe(float* out, long long* cyc, int timing_mmas, int variant) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (base - raw);
-  __shared__ uint64_t bar[2];
+  __shared__ uint64_t bar[4];
   __shared__ uint32_t tmem_slot;
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -98,6 +98,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(160, 1) probe(float*
   if (threadIdx.x == 0) {
     mbar_init(smem_u32(&bar[0]), 1);
     mbar_init(smem_u32(&bar[1]), 1);
+    mbar_init(smem_u32(&bar[2]), 1);
+    mbar_init(smem_u32(&bar[3]), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 4) {
@@ -144,13 +146,31 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(160, 1) probe(float*
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint64_t ad = make_desc(base), bd = make_desc(base + 16384);
     const long long t0 = clock64();
-    if (elect_one()) {
+    if (variant == 9) {  // issue-queue depth: time stamp after every issue of 24 back-to-back MMAs
+      if (elect_one()) {
+        long long ts[24];
+#pragma unroll
+        for (int i = 0; i < 24; ++i) {
+          tc_mma2_f16(tmem_base, ad + 2 * (i & 3), bd + 2 * (i & 3), idesc, 1u);
+          ts[i] = clock64();
+        }
+        tc_commit2(smem_u32(&bar[1]));
+        if (blockIdx.x == 0)
+          for (int i = 0; i < 24; ++i) cyc[1 + i] = ts[i] - t0;
+      }
+    } else if (elect_one()) {
       for (int i = 0; i < timing_mmas; i += 4) {
-        const uint32_t d = tmem_base + (uint32_t)((i >> 2) & 1) * 256u;
-        tc_mma2_f16(d, ad, bd, idesc, 1u);
-        tc_mma2_f16(d, ad + 2, bd + 2, idesc, 1u);
-        tc_mma2_f16(d, ad + 4, bd + 4, idesc, 1u);
-        tc_mma2_f16(d, ad + 6, bd + 6, idesc, 1u);
+        const uint32_t blk = (uint32_t)(i >> 2);
+        const uint32_t d = tmem_base + ((blk >> 2) & 1u) * 256u;
+        // variant >= 1: operands rotate over 64 KiB of A (base + 32 KiB..) and a four-stage B ring (base + 96 KiB..)
+        const uint64_t a2 = variant >= 1 ? make_desc(base + 32768 + (blk & 3u) * 16384u) : ad;
+        const uint64_t b2 = variant >= 1 ? make_desc(base + 98304 + ((blk * 5u) & 3u) * 16384u) : bd;
+        tc_mma2_f16(d, a2, b2, idesc, 1u);
+        tc_mma2_f16(d, a2 + 2, b2 + 2, idesc, 1u);
+        tc_mma2_f16(d, a2 + 4, b2 + 4, idesc, 1u);
+        tc_mma2_f16(d, a2 + 6, b2 + 6, idesc, 1u);
+        if (variant >= 2) tc_commit2(smem_u32(&bar[2]));  // nobody waits on these: cost of the commit itself
+        if (variant >= 3) tc_commit2(smem_u32(&bar[3]));
       }
       tc_commit2(smem_u32(&bar[1]));
     }
@@ -171,12 +191,12 @@ int main() {
   float* d_out;
   long long* d_cyc;
   cudaMalloc(&d_out, 256 * 256 * 4);
-  cudaMalloc(&d_cyc, 8);
+  cudaMalloc(&d_cyc, 8 * 32);
   cudaMemset(d_out, 0, 256 * 256 * 4);
-  const int smem = 32768 + 1024;
+  const int smem = 98304 + 65536 + 1024;
   cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   const int n = 512;
-  probe<<<148, 160, smem>>>(d_out, d_cyc, n);
+  probe<<<148, 160, smem>>>(d_out, d_cyc, n, 0);
   cudaError_t e = cudaDeviceSynchronize();
   printf("launch: %s\n", cudaGetErrorString(e));
   if (e != cudaSuccess) return 1;
@@ -196,5 +216,21 @@ int main() {
     }
   printf("cta_group::2 M256 N256 K64: max |err| = %g, mismatches = %d; %.1f clk per MMA (%d MMAs, ideal 128)\n", worst, bad,
          (double)cyc / n, n);
+  for (int variant = 0; variant < 4; ++variant)
+    for (int nn : {512, 16384}) {
+      probe<<<148, 160, smem>>>(d_out, d_cyc, nn, variant);
+      e = cudaDeviceSynchronize();
+      cudaMemcpy(&cyc, d_cyc, 8, cudaMemcpyDeviceToHost);
+      printf("variant %d (%s), %5d MMAs: %.1f clk per MMA %s\n", variant,
+             variant == 0 ? "fixed operands" : variant == 1 ? "rotating operands" : variant == 2 ? "rotating + commit per 4" : "rotating + 2 commits per 4",
+             nn, (double)cyc / nn, e == cudaSuccess ? "" : cudaGetErrorString(e));
+    }
+  probe<<<148, 160, smem>>>(d_out, d_cyc, 24, 9);
+  cudaDeviceSynchronize();
+  long long ts[32];
+  cudaMemcpy(ts, d_cyc, sizeof(ts), cudaMemcpyDeviceToHost);
+  printf("clock after issuing MMA i (24 back to back, total %lld):", ts[0]);
+  for (int i = 0; i < 24; ++i) printf(" %lld", ts[1 + i]);
+  printf("\n");
   return 0;
 }

@@ -18,10 +18,10 @@ r.fine.forward_batch(pts, dirs, precision="fp16")  # warm
 os.environ["NERF_B200_TRACE"] = path
 r.fine.forward_batch(pts, dirs, precision="fp16")
 del os.environ["NERF_B200_TRACE"]
-raw = np.fromfile(path, np.uint64).reshape(6, 2048, 2)
-names = ["mma", "tma", "epiX0", "epiX1", "epiY0", "epiY1"]
-t0 = min(int(raw[k, 0, 1]) for k in range(6) if raw[k, 0, 1])
-for k in range(6):
+raw = np.fromfile(path, np.uint64).reshape(7, 2048, 2)
+names = ["mma", "tma", "epiX0", "epiX1", "epiY0", "epiY1", "relay"]
+t0 = min(int(raw[k, 0, 1]) for k in range(7) if raw[k, 0, 1])
+for k in range(7):
     ev = [(int(t) - t0, int(tag)) for tag, t in raw[k] if t]
     print(names[k], len(ev))
     print(" ".join(f"{tag:03x}@{t}" for t, tag in ev[:int(sys.argv[1]) if len(sys.argv) > 1 else 120]))
