@@ -19,10 +19,11 @@
 //   - concat_rows(h0, h4) (network.rs:210) is split-K: the PE tile (K = 64) and h4 (K = 256) accumulate into
 //     the same D.  concat_rows(bottleneck, PE4(dir)) (network.rs:220) likewise (K = 256 + 32).
 //   - sigma (256 -> 1) and rgb (128 -> 3) heads are f32 dot products in the epilogue on the f32 accumulators.
-// Warp roles (both CTAs): warp 0 = TMA producer of the CTA's weight halves, warp 1 = MMA issuer (leader CTA only,
-// one elected lane), warp 2 = TMEM allocator, warp 3 = relay ("my half of chunk g has landed" -> leader),
-// warps 4..11 = epilogue of slot X, warps 12..19 = epilogue of slot Y (warp % 4 = TMEM lane quadrant, two warps
-// per quadrant split the 256 columns).
+// Warp roles (both CTAs): warps 0..15 = epilogue (warp % 4 = TMEM lane quadrant, warp / 4 = column quarter; all
+// sixteen drain slot X's and slot Y's accumulators alternately), warp 16 = TMA producer of the CTA's weight halves,
+// warp 17 = MMA issuer (leader CTA only, one elected lane), warp 18 = TMEM allocator, warp 19 = relay ("my half of
+// chunk g has landed" -> leader).  The control warps have the highest warp ids because the warp schedulers pick
+// the highest eligible warp id first.
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
@@ -38,8 +39,10 @@ namespace nerf {
 namespace {
 
 constexpr int kTileM = 128;
-constexpr int kThreads = 640;            // 4 control warps + 16 epilogue warps
-constexpr int kEpiThreadsPerSlot = 256;  // 8 warps: 4 TMEM lane quadrants x 2 column halves
+constexpr int kThreads = 640;  // 16 epilogue warps + 4 control warps
+// The SM's warp schedulers favour the highest warp id among eligible warps, so the control warps sit above the
+// epilogue warps: an MMA issue, a TMA launch or a relay signal never queues behind conversion arithmetic.
+constexpr int kEpiWarps = 16, kWarpTma = 16, kWarpMma = 17, kWarpAlloc = 18, kWarpRelay = 19;
 constexpr int kStages = 4;
 constexpr uint32_t kStageBytes = 128 * 128;      // this CTA's N-half of a chunk: [128 x 64] 16-bit
 constexpr uint32_t kKBlockBytes = kTileM * 128;  // one [128 x 64] K-block of an A tile
@@ -256,27 +259,24 @@ struct Tracer {
   }
 };
 // ------------------------------------------------------------------------------------------ epilogue pieces
-// A 256-wide layer is drained by 8 warps per tile slot: warp (quad, half) owns TMEM lanes 32*quad..+31
-// (one sample row per thread) and columns 128*half..+127, as four 32-column blocks.  TMEM loads are software
-// pipelined: block b+1 is in flight while block b is converted and stored.
-// One 32-column block of the accumulator: optional f32 bias (layers without a PE chunk; the others carry it through
-// the ones column), optional sigma partial on the unrounded f32 values; optional ReLU + 16-bit store into the next
-// layer's A tile.  `bias` and `walpha` point into the kernel's constant bank (warp-uniform operands).
-template <bool kFp16, bool kRelu, bool kSigma, bool kStore, bool kBias>
+// All 16 epilogue warps drain whichever slot's accumulator completes next (X and Y alternate): warp (quad, colq)
+// owns TMEM lanes 32*quad..+31 (one sample row per thread) and columns 64*colq..+63 of both slots = K-block colq
+// of the next layer's A tile, as two 32-column blocks.
+// One 32-column block: f32 bias, optional sigma partial on the unrounded f32 values, optional ReLU + 16-bit store.
+// `bias` and `walpha` point into the kernel's constant bank (warp-uniform operands, no loads).
+template <bool kFp16, bool kRelu, bool kSigma, bool kStore>
 __device__ __forceinline__ void epi_block(uint32_t (&v)[32], const float* __restrict__ bias,
-                                          const float* __restrict__ walpha, float& sig, uint8_t* act_row, uint32_t r8,
-                                          int cb) {
-  if constexpr (kBias) {
+                                          const float* __restrict__ walpha, float& sig, uint8_t* kblock_row,
+                                          const uint32_t (&swz)[8], int chunk0) {
+#ifndef NERF_EXP_NOBIAS
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + bias[cb * 32 + j]);
-  }
+  for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + bias[j]);
+#endif
   if constexpr (kSigma) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) sig = fmaf(fmaxf(__uint_as_float(v[j]), 0.0f), walpha[cb * 32 + j], sig);
+    for (int j = 0; j < 32; ++j) sig = fmaf(fmaxf(__uint_as_float(v[j]), 0.0f), walpha[j], sig);
   }
   if constexpr (kStore) {
-    uint8_t* kblock = act_row + (cb >> 1) * kKBlockBytes;
-    const uint32_t chunk0 = (cb & 1) * 4;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       uint4 q;
@@ -284,51 +284,76 @@ __device__ __forceinline__ void epi_block(uint32_t (&v)[32], const float* __rest
       q.y = pack2<kFp16, kRelu>(__uint_as_float(v[i * 8 + 2]), __uint_as_float(v[i * 8 + 3]));
       q.z = pack2<kFp16, kRelu>(__uint_as_float(v[i * 8 + 4]), __uint_as_float(v[i * 8 + 5]));
       q.w = pack2<kFp16, kRelu>(__uint_as_float(v[i * 8 + 6]), __uint_as_float(v[i * 8 + 7]));
-      *reinterpret_cast<uint4*>(kblock + (((chunk0 + i) ^ r8) << 4)) = q;
+#ifdef NERF_EXP_NOSTS
+      if (q.x == 0x12345678u)
+#endif
+      *reinterpret_cast<uint4*>(kblock_row + swz[chunk0 + i]) = q;
     }
   }
 }
 
-// Four 32-column blocks starting at block cb0, TMEM loads double-buffered.
-template <bool kFp16, bool kRelu, bool kSigma, bool kStore, bool kBias>
-__device__ __forceinline__ void epi_layer(Tracer& tr, uint32_t taddr, const float* __restrict__ bias,
-                                          const float* __restrict__ walpha, float& sig, uint8_t* act_row, uint32_t r8,
-                                          int cb0) {
+// The warp's 64 columns of one slot-layer; bias / walpha already point at the warp's first column.
+template <bool kFp16, bool kRelu, bool kSigma, bool kStore>
+__device__ __forceinline__ void epi_cols(Tracer& tr, uint32_t taddr, const float* __restrict__ bias, const float* __restrict__ walpha,
+                                         float& sig, uint8_t* kblock_row, const uint32_t (&swz)[8]) {
   uint32_t va[32], vb[32];
-  const uint32_t t0 = taddr + cb0 * 32;
-  tc_ld32(t0, va);
-  tc_ld32(t0 + 32, vb);
+#ifdef NERF_EXP_NOLDTM
+#pragma unroll
+  for (int j = 0; j < 32; ++j) va[j] = vb[j] = taddr + j;
+#else
+  tc_ld32(taddr, va);
+  tc_ld32(taddr + 32, vb);
   tc_wait_ld();
-  tr.rec(0x600);
-  epi_block<kFp16, kRelu, kSigma, kStore, kBias>(va, bias, walpha, sig, act_row, r8, cb0);
-  tc_ld32(t0 + 64, va);
-  epi_block<kFp16, kRelu, kSigma, kStore, kBias>(vb, bias, walpha, sig, act_row, r8, cb0 + 1);
-  tc_ld32(t0 + 96, vb);
-  tc_wait_ld();
-  tr.rec(0x700);
-  epi_block<kFp16, kRelu, kSigma, kStore, kBias>(va, bias, walpha, sig, act_row, r8, cb0 + 2);
-  epi_block<kFp16, kRelu, kSigma, kStore, kBias>(vb, bias, walpha, sig, act_row, r8, cb0 + 3);
+#endif
+  epi_block<kFp16, kRelu, kSigma, kStore>(va, bias, walpha, sig, kblock_row, swz, 0);
+  epi_block<kFp16, kRelu, kSigma, kStore>(vb, bias + 32, walpha + 32, sig, kblock_row, swz, 4);
 }
 
-// positional_encoding_* (network.rs:263-330): octaves [o0, o1) of one sample into row `row` of an aux tile.
-template <bool kFp16>
-__device__ __forceinline__ void write_octaves(uint8_t* aux, uint32_t row, const float v[3], int o0, int o1) {
-#pragma unroll 1
-  for (int o = o0; o < o1; ++o) {
-    const float f = (float)(1 << o);  // f doubles per octave (network.rs:287)
+// positional_encoding_* (network.rs:263-330): columns [kCol0, kCol0 + 16) of one sample's encoding with kOctaves
+// octaves, as two 16-byte chunks of row `row` of an aux tile.  Column layout: 0..2 = v, 3 + 6o + a = sin(2^o v_a),
+// 6 + 6o + a = cos(2^o v_a), zero padding after 3 + 6 * kOctaves.  The lowest octave the 16 columns touch is
+// evaluated with fast_sincos; the (at most three) following ones by angle doubling, sin 2x = 2 sin x cos x and
+// cos 2x = 1 - 2 sin^2 x, which adds ~1e-6 absolute error - far below the operand's 16-bit rounding.
+template <bool kFp16, int kCol0, int kOctaves>
+__device__ __forceinline__ void write_pe16(uint8_t* aux_row, uint32_t r8, const float (&v)[3]) {
+  constexpr int kEnd = 3 + 6 * kOctaves;
+  constexpr int kLo = kCol0 < 3 ? 0 : (kCol0 - 3) / 6;
+  constexpr int kHiCol = (kCol0 + 15 < kEnd ? kCol0 + 15 : kEnd - 1);
+  constexpr int kHi = kHiCol < 3 ? -1 : (kHiCol - 3) / 6;
+  constexpr int kN = kHi >= kLo ? kHi - kLo + 1 : 0;
+  float sn[kN > 0 ? kN : 1][3], cs[kN > 0 ? kN : 1][3];
+  if constexpr (kN > 0) {
 #pragma unroll
-    for (int a = 0; a < 3; ++a) {
-      float sv, cv;
-      fast_sincos(f * v[a], sv, cv);
-      *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, 3 + 6 * o + a)) = cvt1<kFp16>(sv);
-      *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, 6 + 6 * o + a)) = cvt1<kFp16>(cv);
+    for (int a = 0; a < 3; ++a) fast_sincos((float)(1 << kLo) * v[a], sn[0][a], cs[0][a]);  // f doubles per octave (network.rs:287)
+#pragma unroll
+    for (int i = 1; i < kN; ++i) {
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        sn[i][a] = 2.0f * sn[i - 1][a] * cs[i - 1][a];
+        cs[i][a] = fmaf(-2.0f * sn[i - 1][a], sn[i - 1][a], 1.0f);
+      }
     }
   }
-}
-template <bool kFp16>
-__device__ __forceinline__ void write_raw3(uint8_t* aux, uint32_t row, const float v[3]) {
+  float out[16];
 #pragma unroll
-  for (int a = 0; a < 3; ++a) *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, a)) = cvt1<kFp16>(v[a]);
+  for (int j = 0; j < 16; ++j) {
+    const int col = kCol0 + j;
+    if (col < 3) out[j] = v[col];
+    else if (col >= kEnd) out[j] = 0.0f;
+    else {
+      const int o = (col - 3) / 6 - kLo, k = (col - 3) % 6;
+      out[j] = k < 3 ? sn[o][k] : cs[o][k - 3];
+    }
+  }
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    uint4 q;
+    q.x = pack2<kFp16, false>(out[8 * h + 0], out[8 * h + 1]);
+    q.y = pack2<kFp16, false>(out[8 * h + 2], out[8 * h + 3]);
+    q.z = pack2<kFp16, false>(out[8 * h + 4], out[8 * h + 5]);
+    q.w = pack2<kFp16, false>(out[8 * h + 6], out[8 * h + 7]);
+    *reinterpret_cast<uint4*>(aux_row + ((((uint32_t)(kCol0 / 8 + h)) ^ r8) << 4)) = q;
+  }
 }
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
@@ -367,11 +392,11 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_acc + 8 * s, 1);
-      mbar_init(bar_act + 8 * s, 16);   // leader only: one elected arrive per epilogue warp of the slot, both CTAs
+      mbar_init(bar_act + 8 * s, 32);   // leader only: one elected arrive per epilogue warp, both CTAs
     }
     fence_barrier_init();
   }
-  if (warp == 2) {
+  if (warp == kWarpAlloc) {
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(base + kOffBar + kTmemSlotOff),
                  "r"(512u)
                  : "memory");
@@ -386,7 +411,7 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
   int n_chunks_quad = 0;
   for (int l = 0; l < n_layers; ++l) n_chunks_quad += layer_chunks(l);
 
-  if (warp == 0) {
+  if (warp == kWarpTma) {
     // ===================================================== TMA producer: this CTA's half of every weight chunk
     Tracer tr{(trace != nullptr && blockIdx.x == 0 && lane == 0) ? trace + 1 * 2 * kTraceCap : nullptr, 0};
     uint32_t stage = 0, phase = 0;
@@ -408,7 +433,7 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
         }
       }
     }
-  } else if (warp == 3) {
+  } else if (warp == kWarpRelay) {
     // ===================================================== relay: tell the leader that this CTA's half has landed
     Tracer tr{(trace != nullptr && blockIdx.x == 0 && lane == 0) ? trace + 6 * 2 * kTraceCap : nullptr, 0};
     uint32_t stage = 0, phase = 0;
@@ -425,7 +450,7 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == kWarpMma) {
     // ===================================================== MMA issuer (leader CTA): one thread drives both tensor cores
     if (rank == 0) {
       Tracer tr{(trace != nullptr && blockIdx.x == 0 && lane == 0) ? trace : nullptr, 0};
@@ -486,156 +511,205 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
         }
       }
     }
-  } else if (warp >= 4) {
-    // ===================================================== epilogue warps: one thread per (sample row, column half)
-    const int ew = warp - 4;
-    const int slot = ew >> 3;
-    const int half = (ew >> 2) & 1;
+  } else if (warp < kEpiWarps) {
+    // ===================================================== epilogue warps: one thread per (sample row, column quarter)
+    const int colq = warp >> 2;
     const uint32_t quad = (uint32_t)(warp & 3);
     const uint32_t row = quad * 32u + (uint32_t)lane;
     const uint32_t r8 = row & 7u;
-    const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + (uint32_t)slot * 256u;
-    uint8_t* act_row = smem + kOffAct + slot * kActBytes + (row >> 3) * 1024u + r8 * 128u;
-    uint8_t* aux = smem + kOffAux + slot * kAuxBytes;
-    // f32 scratch for combining the two column halves of a row: aux columns 32..63 are free whenever it is used
-    float* scratch = reinterpret_cast<float*>(aux + sw128_offset(row, 32));       // sigma partial (16 B chunk)
-    float* scratch2 = reinterpret_cast<float*>(aux + sw128_offset(row, 40));      // rgb partials
-    const uint32_t pair_bar = 1u + (uint32_t)slot * 4u + quad;                    // named barrier of the 2 warps of a row
-    const uint32_t acc_bar = bar_acc + 8 * slot, act_bar = bar_act + 8 * slot;
-    const int cb0 = half * 4;
-    uint32_t acc_par = 0;
-    Tracer tr{(trace != nullptr && blockIdx.x == 0 && quad == 0 && lane == 0) ? trace + (2 + slot * 2 + half) * 2 * kTraceCap
-                                                                             : nullptr, 0};
-    for (int64_t qd = pair_id; qd < n_quads; qd += n_pairs) {
-      // tiles past the end run through the same barrier protocol on zero inputs and store nothing
-      const int64_t tile = 4 * qd + 2 * slot + (int64_t)rank;
-      tr.rec(0x500);
-      const int64_t g = tile * kTileM + row;
-      const bool valid = g < src.B;
-      float p[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 0.f};
-      if (valid) {
-        if (src.mode == 0) {
-          p[0] = src.points[g];
-          p[1] = src.points[src.B + g];
-          p[2] = src.points[2 * src.B + g];
-          d[0] = src.dirs[g * 3 + 0];
-          d[1] = src.dirs[g * 3 + 1];
-          d[2] = src.dirs[g * 3 + 2];
-        } else {
-          const int64_t ray = g / src.S;
-          d[0] = src.dirs[ray * 3 + 0];
-          d[1] = src.dirs[ray * 3 + 1];
-          d[2] = src.dirs[ray * 3 + 2];
-          const float t = src.t[g];
-          p[0] = __fadd_rn(src.origin[0], __fmul_rn(d[0], t));  // origin + dir_hat * t (lib.rs:396,436)
-          p[1] = __fadd_rn(src.origin[1], __fmul_rn(d[1], t));
-          p[2] = __fadd_rn(src.origin[2], __fmul_rn(d[2], t));
-        }
-      }
-      // PE10(p): layer-0 / skip operand (network.rs:204); the two halves split the octaves
-      if (half == 0) {
-        write_raw3<kFp16>(aux, row, p);
-        write_octaves<kFp16>(aux, row, p, 0, 5);
-      } else {
-        write_octaves<kFp16>(aux, row, p, 5, 10);
-        *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, 63)) = 0;  // K padding (weight row 63 is zero too)
-      }
+    const uint32_t taddr0 = tmem_base + ((quad * 32u) << 16) + (uint32_t)colq * 64u;  // + 256 * slot
+    // this row of K-block colq of slot 0's A tile; slot 1's is kActBytes further
+    uint8_t* const kblock_row0 = smem + kOffAct + (uint32_t)colq * kKBlockBytes + (row >> 3) * 1024u + r8 * 128u;
+    uint32_t swz[8];  // byte offset of 16-byte chunk c inside the row's 128 bytes (SWIZZLE_128B)
+#pragma unroll
+    for (uint32_t c = 0; c < 8; ++c) swz[c] = (c ^ r8) << 4;
+    // f32 scratch for combining the four column quarters of a row: quarter k >= 1 owns the 16-byte chunk at aux
+    // column 32 + 8k = {rgb partials, sigma partial}; aux columns 32..63 are free whenever it is used
+    const uint32_t scratch_off = sw128_offset(row, 32u + 8u * (uint32_t)colq);
+    const uint32_t row_bar = 1u + quad;  // named barrier of the 4 warps (128 threads) that share a row
+    uint32_t acc_par = 0;                // bit s: parity of slot s's "accumulator complete" barrier
+    Tracer tr{(trace != nullptr && blockIdx.x == 0 && quad == 0 && lane == 0) ? trace + (2 + colq) * 2 * kTraceCap : nullptr, 0};
+
+    auto acc_wait = [&](int s) {
+      mbar_wait(bar_acc + 8 * s, (acc_par >> s) & 1u);
+      acc_par ^= 1u << s;
+      tc_fence_after();
+    };
+    auto act_ready = [&](int s) {  // this warp's part of slot s's next A operand is in shared memory, its columns drained
       fence_proxy_async();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
+      if (lane == 0) mbar_arrive_cluster(bar_act + 8 * s, 0u);  // one arrive per warp on the leader's barrier
+    };
+
+    // The next quad's inputs are fetched two layers before they are needed: {p.xyz, -} for explicit points,
+    // {dir.xyz, t} for samples along rays.  Tiles past the end run the same barrier protocol on zeros.
+    float4 pre[2];
+    auto prefetch = [&](int64_t qd) {
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        const int64_t gi = (4 * qd + 2 * s + (int64_t)rank) * kTileM + row;
+        pre[s] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (gi < src.B) {
+          if (src.mode == 0) {
+            pre[s] = make_float4(src.points[gi], src.points[src.B + gi], src.points[2 * src.B + gi], 0.f);
+          } else {
+            const int64_t ray = gi / src.S;
+            pre[s] = make_float4(src.dirs[ray * 3 + 0], src.dirs[ray * 3 + 1], src.dirs[ray * 3 + 2], src.t[gi]);
+          }
+        }
+      }
+    };
+    prefetch(pair_id);
+    for (int64_t qd = pair_id; qd < n_quads; qd += n_pairs) {
+      int64_t g[2];
+      bool valid[2];
+      float dir[2][3];
+      tr.rec(0x500);
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        const int64_t tile = 4 * qd + 2 * s + (int64_t)rank;
+        g[s] = tile * kTileM + row;
+        valid[s] = g[s] < src.B;
+        float p[3] = {pre[s].x, pre[s].y, pre[s].z};
+        dir[s][0] = dir[s][1] = dir[s][2] = 0.f;
+        if (src.mode == 0) {
+          if (valid[s]) {  // not needed before the bottleneck layer: the load stays in flight
+            dir[s][0] = src.dirs[g[s] * 3 + 0];
+            dir[s][1] = src.dirs[g[s] * 3 + 1];
+            dir[s][2] = src.dirs[g[s] * 3 + 2];
+          }
+        } else {
+          dir[s][0] = pre[s].x;
+          dir[s][1] = pre[s].y;
+          dir[s][2] = pre[s].z;
+          if (valid[s]) {
+            p[0] = __fadd_rn(src.origin[0], __fmul_rn(dir[s][0], pre[s].w));  // origin + dir_hat * t (lib.rs:396,436)
+            p[1] = __fadd_rn(src.origin[1], __fmul_rn(dir[s][1], pre[s].w));
+            p[2] = __fadd_rn(src.origin[2], __fmul_rn(dir[s][2], pre[s].w));
+          }
+        }
+        // PE10(p): layer-0 / skip operand (network.rs:204); each column quarter writes its 16 of the 64 columns
+        uint8_t* aux_row = smem + kOffAux + s * kAuxBytes + (row >> 3) * 1024u + r8 * 128u;
+        if (colq == 0) write_pe16<kFp16, 0, kPosOctaves>(aux_row, r8, p);
+        else if (colq == 1) write_pe16<kFp16, 16, kPosOctaves>(aux_row, r8, p);
+        else if (colq == 2) write_pe16<kFp16, 32, kPosOctaves>(aux_row, r8, p);
+        else write_pe16<kFp16, 48, kPosOctaves>(aux_row, r8, p);
+        act_ready(s);
+      }
       tr.rec(0x400);
 
-      float sig = half == 0 ? C.b_alpha : 0.0f;
+      float sig[2];
+      sig[0] = sig[1] = colq == 0 ? C.b_alpha : 0.0f;
 #pragma unroll 1
       for (int l = 0; l < 7; ++l) {
-        tr.rec(0x100 | l);
-        mbar_wait(acc_bar, acc_par);
-        acc_par ^= 1u;
-        tc_fence_after();
-        tr.rec(0x200 | l);
-        epi_layer<kFp16, true, false, true, true>(tr, taddr, C.bias[l], C.w_alpha, sig, act_row, r8, cb0);
-        fence_proxy_async();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
-        tr.rec(0x300 | l);
-      }
-      mbar_wait(acc_bar, acc_par);  // dense7 -> h8; sigma = relu(alpha(h8)) (network.rs:216)
-      acc_par ^= 1u;
-      tc_fence_after();
-      if (want_rgb) {
-        epi_layer<kFp16, true, true, true, true>(tr, taddr, C.bias[7], C.w_alpha, sig, act_row, r8, cb0);
-        fence_proxy_async();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
-      } else {
-        epi_layer<kFp16, true, true, false, true>(tr, taddr, C.bias[7], C.w_alpha, sig, act_row, r8, cb0);
-        tc_fence_before();
-      }
-      if (half == 1) scratch[0] = sig;
-      named_bar_sync(pair_bar, 64);
-      if (half == 0 && valid) dst.sigma[g] = fmaxf(sig + scratch[0], 0.0f);
-      named_bar_sync(pair_bar, 64);  // scratch lives in aux columns the other half overwrites next
-      if (want_rgb) {
-        mbar_wait(acc_bar, acc_par);  // bottleneck, ActivationType::None (network.rs:218)
-        acc_par ^= 1u;
-        tc_fence_after();
-        epi_layer<kFp16, false, false, true, true>(tr, taddr, C.bias[8], C.w_alpha, sig, act_row, r8, cb0);
-        // PE4(dir) replaces PE10(p) in the aux tile: the skip MMA that read it finished layers ago
-        if (half == 0) {
-          write_raw3<kFp16>(aux, row, d);
-          write_octaves<kFp16>(aux, row, d, 0, 2);
-        } else {
-          write_octaves<kFp16>(aux, row, d, 2, 4);
-          for (int k = kDirEnc; k < 32; ++k) *reinterpret_cast<uint16_t*>(aux + sw128_offset(row, k)) = 0;  // K padding to 32
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          tr.rec(0x100 | l | (s << 12));
+          acc_wait(s);
+          tr.rec(0x200 | l | (s << 12));
+          epi_cols<kFp16, true, false, true>(tr, taddr0 + 256u * s, C.bias[l] + colq * 64, C.w_alpha, sig[s],
+                                             kblock_row0 + s * kActBytes, swz);
+          act_ready(s);
+          tr.rec(0x300 | l | (s << 12));
         }
-        fence_proxy_async();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(act_bar, 0u);  // one arrive per warp on the leader's barrier
-
-        mbar_wait(acc_bar, acc_par);  // viewdirs (ReLU) then the f32 rgb head + sigmoid (network.rs:222-223)
-        acc_par ^= 1u;
-        tc_fence_after();
-        float r0 = 0.f, r1 = 0.f, r2 = 0.f;
-        if (half == 0) { r0 = C.b_rgb[0]; r1 = C.b_rgb[1]; r2 = C.b_rgb[2]; }
-#pragma unroll 1
-        for (int cb = half * 2; cb < half * 2 + 2; ++cb) {
+      }
+      if (qd + n_pairs < n_quads) prefetch(qd + n_pairs);
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {  // dense7 -> h8; sigma = relu(alpha(h8)) (network.rs:216)
+        acc_wait(s);
+        if (want_rgb) {
+          epi_cols<kFp16, true, true, true>(tr, taddr0 + 256u * s, C.bias[7] + colq * 64, C.w_alpha + colq * 64, sig[s],
+                                            kblock_row0 + s * kActBytes, swz);
+          act_ready(s);
+        } else {
+          epi_cols<kFp16, true, true, false>(tr, taddr0 + 256u * s, C.bias[7] + colq * 64, C.w_alpha + colq * 64, sig[s],
+                                             kblock_row0 + s * kActBytes, swz);
+          tc_fence_before();
+        }
+        float* scratch = reinterpret_cast<float*>(smem + kOffAux + s * kAuxBytes + scratch_off);
+        if (colq != 0) scratch[3] = sig[s];
+      }
+      named_bar_sync(row_bar, 128);
+      if (colq == 0) {
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          const uint8_t* aux = smem + kOffAux + s * kAuxBytes;
+          float v = sig[s];
+#pragma unroll
+          for (uint32_t k = 1; k < 4; ++k) v += reinterpret_cast<const float*>(aux + sw128_offset(row, 32u + 8u * k))[3];
+          if (valid[s]) dst.sigma[g[s]] = fmaxf(v, 0.0f);
+        }
+      }
+      if (want_rgb) {
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {  // bottleneck, ActivationType::None (network.rs:218)
+          acc_wait(s);
+          epi_cols<kFp16, false, false, true>(tr, taddr0 + 256u * s, C.bias[8] + colq * 64, C.w_alpha, sig[s],
+                                              kblock_row0 + s * kActBytes, swz);
+          // PE4(dir) replaces PE10(p) in the aux tile (columns 0..31): the skip MMA that read it finished layers ago
+          uint8_t* aux_row = smem + kOffAux + s * kAuxBytes + (row >> 3) * 1024u + r8 * 128u;
+          if (colq == 0) write_pe16<kFp16, 0, kDirOctaves>(aux_row, r8, dir[s]);
+          else if (colq == 1) write_pe16<kFp16, 16, kDirOctaves>(aux_row, r8, dir[s]);  // columns 27..31: K padding
+          act_ready(s);
+        }
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {  // viewdirs (ReLU) then the f32 rgb head (network.rs:222-223): 32 columns per warp
+          acc_wait(s);
           uint32_t v[32];
-          tc_ld32(taddr + cb * 32, v);
+          tc_ld32(tmem_base + ((quad * 32u) << 16) + 256u * s + 32u * (uint32_t)colq, v);
           tc_wait_ld();
+          float r0 = 0.f, r1 = 0.f, r2 = 0.f;
+          if (colq == 0) { r0 = C.b_rgb[0]; r1 = C.b_rgb[1]; r2 = C.b_rgb[2]; }
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
-            const int k = cb * 32 + j;
+            const int k = colq * 32 + j;
             const float c = fmaxf(__uint_as_float(v[j]) + C.bias[9][k], 0.0f);
             r0 = fmaf(c, C.w_rgb[k * 3 + 0], r0);
             r1 = fmaf(c, C.w_rgb[k * 3 + 1], r1);
             r2 = fmaf(c, C.w_rgb[k * 3 + 2], r2);
           }
+          tc_fence_before();
+          float* scratch = reinterpret_cast<float*>(smem + kOffAux + s * kAuxBytes + scratch_off);
+          if (colq != 0) {
+            scratch[0] = r0;
+            scratch[1] = r1;
+            scratch[2] = r2;
+          } else {
+            sig[s] = r0;  // quarter 0 keeps its partials in registers until the others have written theirs
+            dir[s][0] = r1;
+            dir[s][1] = r2;
+          }
         }
-        tc_fence_before();
-        if (half == 1) {
-          scratch2[0] = r0;
-          scratch2[1] = r1;
-          scratch2[2] = r2;
+        named_bar_sync(row_bar, 128);
+        if (colq == 0) {
+#pragma unroll
+          for (int s = 0; s < 2; ++s) {
+            const uint8_t* aux = smem + kOffAux + s * kAuxBytes;
+            float r0 = sig[s], r1 = dir[s][0], r2 = dir[s][1];
+#pragma unroll
+            for (uint32_t k = 1; k < 4; ++k) {
+              const float* sc = reinterpret_cast<const float*>(aux + sw128_offset(row, 32u + 8u * k));
+              r0 += sc[0];
+              r1 += sc[1];
+              r2 += sc[2];
+            }
+            if (valid[s]) {
+              dst.rgb[g[s] * 3 + 0] = 1.0f / (1.0f + expf(-r0));  // network.rs:165
+              dst.rgb[g[s] * 3 + 1] = 1.0f / (1.0f + expf(-r1));
+              dst.rgb[g[s] * 3 + 2] = 1.0f / (1.0f + expf(-r2));
+            }
+          }
         }
-        named_bar_sync(pair_bar, 64);
-        if (half == 0 && valid) {
-          dst.rgb[g * 3 + 0] = 1.0f / (1.0f + expf(-(r0 + scratch2[0])));  // network.rs:165
-          dst.rgb[g * 3 + 1] = 1.0f / (1.0f + expf(-(r1 + scratch2[1])));
-          dst.rgb[g * 3 + 2] = 1.0f / (1.0f + expf(-(r2 + scratch2[2])));
-        }
-        named_bar_sync(pair_bar, 64);  // scratch is inside the aux tile the next tile's PE overwrites
       }
+      named_bar_sync(row_bar, 128);  // scratch is inside the aux tiles the next quad's PE overwrites
     }
   }
 
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();  // the peer's shared memory and TMEM stay alive until the pair's last MMA has been consumed
-  if (warp == 2) {
+  if (warp == kWarpAlloc) {
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
   }
 }

@@ -42,18 +42,22 @@ __host__ __device__ constexpr uint32_t make_idesc(int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 }
 
-constexpr uint32_t kA = 0, kB = 65536, kW = 65536 + 65536, kTotal = kW + 32768;
+constexpr uint32_t kA = 0, kB = 65536, kW = 65536 + 65536, kT = kW + 32768, kTotal = kT + 32768;
 
 // lsu_mode: 0 none, 1 STS.128 (conflict-free), 2 LDS.128 broadcast, 3 LDS.128 conflict-free
-__global__ void __launch_bounds__(544, 1) probe(int n_mma, int lsu_mode, int lsu_iters, long long* out) {
+__global__ void __launch_bounds__(576, 1) probe(int n_mma, int lsu_mode, int lsu_iters, long long* out,
+                                                const uint8_t* gbuf = nullptr, int n_copies = 0, int workers = 0) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t base = smem_u32(smem);
   __shared__ uint64_t bar;
+  __shared__ uint64_t tbar[2];
   __shared__ uint32_t tmem_slot;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < (int)(kTotal / 4); i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
   if (threadIdx.x == 0) {
     mbar_init(smem_u32(&bar), 1);
+    mbar_init(smem_u32(&tbar[0]), 1);
+    mbar_init(smem_u32(&tbar[1]), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {
@@ -83,7 +87,27 @@ __global__ void __launch_bounds__(544, 1) probe(int n_mma, int lsu_mode, int lsu
       const long long t1 = clock64();
       if (blockIdx.x == 0) out[0] = t1 - t0;
     }
-  } else if (lsu_mode != 0) {
+  } else if (n_copies > 0 && warp == workers + 1) {
+    // 16 KiB bulk copies (two in flight) of an L2-resident buffer, as the weight ring does
+    if (lane == 0) {
+      size_t off = 0;
+      const long long t0 = clock64();
+      for (int i = 0; i < n_copies + 2; ++i) {
+        const int st = i & 1;
+        if (i >= 2) mbar_wait(smem_u32(&tbar[st]), ((i >> 1) - 1) & 1);
+        if (i < n_copies) {
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&tbar[st])), "r"(16384u) : "memory");
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                           base + kT + st * 16384u),
+                       "l"(gbuf + off), "r"(16384u), "r"(smem_u32(&tbar[st]))
+                       : "memory");
+          off = (off + 16384) % (1280 * 1024);
+        }
+      }
+      const long long t1 = clock64();
+      if (blockIdx.x == 0) out[40] = t1 - t0;
+    }
+  } else if (lsu_mode != 0 && warp <= workers) {
     const uint32_t w = (uint32_t)(warp - 1);
     // each warp owns a 512 B row group per iteration; 16 B per lane: conflict-free 128-bit accesses
     const uint32_t my = base + kW + ((w * 2048u) & 32767u) + (uint32_t)lane * 16u;
@@ -161,6 +185,25 @@ int main() {
       }
     }
   }
+  // three-way: MMA operand reads + STS stream + TMA copies into shared memory
+  uint8_t* gbuf;
+  cudaMalloc(&gbuf, 1280 * 1024);
+  cudaMemset(gbuf, 0, 1280 * 1024);
+  for (int with_mma : {0, 1})
+    for (int with_sts : {0, 1}) {
+      const int workers = 16, n_copies = 600;
+      const int iters = with_sts ? 250000 / (workers * 4 * 4) : 0;
+      cudaMemset(d, 0, 64 * 8);
+      probe<<<148, 32 * (2 + workers), kTotal>>>(with_mma ? n_mma : 0, with_sts ? 1 : 0, iters, d, gbuf, n_copies, workers);
+      cudaError_t e = cudaDeviceSynchronize();
+      long long h[64];
+      cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
+      printf("TMA 16 KiB copies x2 in flight%s%s: %.0f clk per copy", with_mma ? " + MMA" : "", with_sts ? " + 16 warps STS.128" : "",
+             (double)h[40] / n_copies);
+      if (with_mma) printf(", %.1f clk/MMA", (double)h[0] / n_mma);
+      if (with_sts) printf(", STS %.1f B/clk", (double)workers * iters * 4 * 512 / h[1]);
+      printf(" %s\n", e == cudaSuccess ? "" : cudaGetErrorString(e));
+    }
   cudaMemset(d, 0, 64 * 8);
   probe<<<148, 32, kTotal>>>(n_mma, 0, 0, d);
   cudaDeviceSynchronize();

@@ -19,7 +19,7 @@ os.environ["NERF_B200_TRACE"] = path
 r.fine.forward_batch(pts, dirs, precision="fp16")
 del os.environ["NERF_B200_TRACE"]
 raw = np.fromfile(path, np.uint64).reshape(7, 2048, 2)
-names = ["mma", "tma", "epiX0", "epiX1", "epiY0", "epiY1", "relay"]
+names = ["mma", "tma", "epi0", "epi1", "epi2", "epi3", "relay"]
 t0 = min(int(raw[k, 0, 1]) for k in range(7) if raw[k, 0, 1])
 for k in range(7):
     ev = [(int(t) - t0, int(tag)) for tag, t in raw[k] if t]
