@@ -30,6 +30,9 @@ FLOP_FINE = 1186816     # full-network sample
 WORKLOAD = "lego 800x800, 64 coarse + 128 fine samples/ray, deterministic sampling, tf_reference camera"
 
 
+NCU_FINE_DRAM_GB = 0.520 + 1.914  # dram__bytes_read.sum + dram__bytes_write.sum, fine pass, 800x800 c64+f128
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -240,7 +243,10 @@ def gpu_arm(args):
                     "d2h_bytes_per_step": n_rays * 12},
             "roofline": {"bound": "tensor", "kernel": "mlp_tc_kernel (fine pass)", "achieved": ach, "peak": sustained,
                          "unit": "TFLOP/s", "frac": ach / sustained, "peak_kind": f"bf16 sustained, {kind}",
-                         "frac_of_burst": ach / burst, "traffic": None},
+                         "frac_of_burst": ach / burst,
+                         # DRAM bytes of the fine-pass launch of one full frame (ncu --set full, read + write,
+                         # profiles/r01_mlp_tc_v15_ncu_full_summary.csv), scaled to this rank's share of the rays
+                         "traffic": NCU_FINE_DRAM_GB * n_local / n_rays, "traffic_unit": "GB per launch (ncu dram read+write)"},
         }
         if world == 1 and not args.no_cpu:
             O, ctx, cores, begin, n = cpu_sample()

@@ -60,9 +60,10 @@ constexpr int kLead = 4;  // chunks of a layer slot X issues before slot Y start
 
 // Layer table: chunks per layer in consumption order.
 constexpr int kNumLayers = 10;  // dense0..7, bottleneck, viewdirs
-// A ring chunk is one [N/2 x 64] weight half per CTA (16 KiB at N = 256, 8 KiB for viewdirs).  dense0 is the PE
-// chunk alone, dense5 the PE chunk + four K-blocks of h4, viewdirs four K-blocks of the bottleneck + the PE4(dir) chunk.
-__host__ __device__ constexpr int layer_chunks(int l) { return l == 0 ? 1 : ((l == 5 || l == 9) ? 5 : 4); }
+// A ring chunk is one [N/2 x 64] weight half per CTA (16 KiB at N = 256).  dense0 is the PE chunk alone, dense5 the
+// PE chunk + four K-blocks of h4; viewdirs (N = 128, 8 KiB halves) packs two K-blocks of the bottleneck per ring
+// stage and ends with the PE4(dir) chunk (K = 32).
+__host__ __device__ constexpr int layer_chunks(int l) { return l == 0 ? 1 : (l == 5 ? 5 : (l == 9 ? 3 : 4)); }
 __host__ __device__ constexpr int layer_n(int l) { return l == 9 ? 128 : 256; }
 
 // ------------------------------------------------------------------------------------------ PTX wrappers
@@ -420,15 +421,18 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
       for (int l = 0; l < n_layers; ++l) {
         const uint32_t bytes = (uint32_t)layer_n(l) * 64u;  // [N/2 x 64] 16-bit
         for (int c = 0; c < layer_chunks(l); ++c) {
+          const uint32_t ncopy = (l == 9 && c < 2) ? 2u : 1u;  // viewdirs: two 8 KiB K-blocks share a stage
           tr.rec(0x100 | l);
           mbar_wait(bar_empty + 8 * stage, phase ^ 1u);
           tr.rec(0x200 | l);
           if (elect_one()) {
-            mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
-            tma_bulk_g2s(base + kOffStage + stage * kStageBytes, src_ptr + rank * bytes, bytes, bar_full + 8 * stage);
+            mbar_arrive_expect_tx(bar_full + 8 * stage, bytes * ncopy);
+            const uint32_t dst_s = base + kOffStage + stage * kStageBytes;
+            tma_bulk_g2s(dst_s, src_ptr + rank * bytes, bytes, bar_full + 8 * stage);
+            if (ncopy == 2) tma_bulk_g2s(dst_s + bytes, src_ptr + (2 + rank) * bytes, bytes, bar_full + 8 * stage);
           }
           __syncwarp();
-          src_ptr += 2 * bytes;
+          src_ptr += 2 * bytes * ncopy;
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
       }
@@ -465,8 +469,9 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
           const uint32_t idesc = make_idesc(kFp16 ? 1 : 0, layer_n(l));
           // the chunk that reads the aux tile (PE10(p) for dense0 / dense5, PE4(dir) last for viewdirs); the others
           // read K-block c - kb_off of the activations
-          const int aux_c = (l == 0 || l == 5) ? 0 : (l == 9 ? 4 : -1);
+          const int aux_c = (l == 0 || l == 5) ? 0 : (l == 9 ? 2 : -1);
           const int kb_off = (l == 5) ? 1 : 0;
+          const int kpc = (l == 9) ? 2 : 1;  // K-blocks per ring chunk
           // Static interleave (X leads Y by kLead chunks): X[0, kLead), Y[0, nch - kLead), X[kLead, nch), Y[rest]:
           // a stage is released early enough for the next layer's load to land, and each slot's epilogue is covered
           // by the other slot's queued MMAs.
@@ -493,13 +498,24 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
               tc_fence_after();
               tr.rec(0x100 | (l << 4) | c | (s << 12));
               const uint64_t bd = stage_desc0 + stage * (kStageBytes >> 4);
-              const uint64_t ad = (c == aux_c) ? auxd : actd + (uint32_t)c * (kKBlockBytes >> 4);
               if (elect_one()) {
-                tc_mma2_f16(d_tmem, ad, bd, idesc, c != 0 ? 1u : 0u);
-                tc_mma2_f16(d_tmem, ad + 2, bd + 2, idesc, 1u);
-                if (!(l == 9 && c == 4)) {  // PE4(dir) is K = 32: aux columns 32..63 hold f32 scratch by then
-                  tc_mma2_f16(d_tmem, ad + 4, bd + 4, idesc, 1u);
-                  tc_mma2_f16(d_tmem, ad + 6, bd + 6, idesc, 1u);
+                if (c == aux_c) {
+                  tc_mma2_f16(d_tmem, auxd, bd, idesc, c != 0 ? 1u : 0u);
+                  tc_mma2_f16(d_tmem, auxd + 2, bd + 2, idesc, 1u);
+                  if (l != 9) {  // PE4(dir) is K = 32: aux columns 32..63 hold f32 scratch by then
+                    tc_mma2_f16(d_tmem, auxd + 4, bd + 4, idesc, 1u);
+                    tc_mma2_f16(d_tmem, auxd + 6, bd + 6, idesc, 1u);
+                  }
+                } else {
+#pragma unroll 1
+                  for (int j = 0; j < kpc; ++j) {
+                    const uint64_t ad = actd + (uint32_t)(c * kpc + j) * (kKBlockBytes >> 4);
+                    const uint64_t bj = bd + (uint32_t)j * (8192u >> 4);
+                    tc_mma2_f16(d_tmem, ad, bj, idesc, (c | j) != 0 ? 1u : 0u);
+                    tc_mma2_f16(d_tmem, ad + 2, bj + 2, idesc, 1u);
+                    tc_mma2_f16(d_tmem, ad + 4, bj + 4, idesc, 1u);
+                    tc_mma2_f16(d_tmem, ad + 6, bj + 6, idesc, 1u);
+                  }
                 }
                 if (c == nch - 1) tc_commit2(bar_acc + 8 * s);  // this layer's accumulator complete -> both epilogues
                 tc_commit2(bar_empty + 8 * stage);               // this slot is done with the chunk (both CTAs' rings)
