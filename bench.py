@@ -217,6 +217,18 @@ def gpu_arm(args):
     clk = clocks.stop() if clocks else {}
     step_e2e()
     e2e_ms, _ = timed(step_e2e, args.steps, False)
+    rgb8_ms = many_ms = None
+    if world == 1:
+        # the same frame returned as 8-bit PPM bytes (3 B/ray over PCIe instead of 12), and a
+        # four-pose sweep whose device-to-host copies overlap the next pose's render
+        def step_rgb8():
+            r.render_rgb8(cam, W, H, NC, NF, precision=args.precision)
+        step_rgb8()
+        rgb8_ms, _ = timed(step_rgb8, max(args.steps // 2, 1), False)
+        cams4 = [cam] * 4
+        def step_many():
+            r.render_many(cams4, W, H, NC, NF, precision=args.precision)
+        many_ms, _ = timed(step_many, 1, False)
 
     if rank == 0:
         import ctypes
@@ -241,6 +253,12 @@ def gpu_arm(args):
             "clocks": clk,
             "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": n_rays * 12},
+            "e2e_rgb8": None if rgb8_ms is None else {
+                "value": n_rays / (rgb8_ms / max(args.steps // 2, 1) * 1e-3), "unit": "rays/s",
+                "d2h_bytes_per_step": n_rays * 3, "api": "nerf_render_rgb8 (device-side save_ppm quantiser)"},
+            "e2e_many": None if many_ms is None else {
+                "value": 4 * n_rays / (many_ms * 1e-3), "unit": "rays/s", "views": 4,
+                "api": "nerf_render_many (pinned double buffer, copies overlap the next view)"},
             "roofline": {"bound": "tensor", "kernel": "mlp_tc_kernel (fine pass)", "achieved": ach, "peak": sustained,
                          "unit": "TFLOP/s", "frac": ach / sustained, "peak_kind": f"bf16 sustained, {kind}",
                          "frac_of_burst": ach / burst,

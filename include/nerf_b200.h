@@ -134,6 +134,22 @@ int nerf_render_device(nerf_ctx*, const nerf_camera*, int W, int H, int n_coarse
 int nerf_render_stages(nerf_ctx*, const nerf_camera*, int W, int H, int n_coarse, int n_fine, int precision,
                        const nerf_sampling*, int64_t ray_begin, int64_t ray_end, float* rgb, const nerf_stages*);
 
+/* The step after the path, on the device: render rays [ray_begin, ray_end) and return 8-bit pixels quantised as
+ * save_ppm does (lib.rs:574-576): channels = 3 gives the PPM body bytes, channels = 4 the RGBA bytes of
+ * pixels_to_rgba (lib.rs:582-592, alpha 255).  3 or 4 B per ray cross PCIe instead of 12. */
+int nerf_render_rgb8(nerf_ctx*, const nerf_camera*, int W, int H, int n_coarse, int n_fine, int precision,
+                     const nerf_sampling*, int64_t ray_begin, int64_t ray_end, int channels, uint8_t* out);
+int nerf_render_rgb8_device(nerf_ctx*, const nerf_camera*, int W, int H, int n_coarse, int n_fine, int precision,
+                            const nerf_sampling*, int64_t ray_begin, int64_t ray_end, int channels, uint8_t* d_out,
+                            void* stream);
+/* Multi-pose batch (an orbit sweep): n_views whole frames of the same size, out = [n_views][H*W][channels] on the
+ * host.  The device-to-host copy of view v (pinned double buffer, own stream) overlaps the render of view v + 1.
+ * Sampling: deterministic or Philox (view v uses seed + v); caller-supplied arrays are not accepted here. */
+int nerf_render_many(nerf_ctx*, const nerf_camera* cams, int n_views, int W, int H, int n_coarse, int n_fine,
+                     int precision, const nerf_sampling*, int channels, uint8_t* out);
+/* The quantiser alone on the device (host buffers): rgb [n_pixels][3] f32 -> out [n_pixels][channels]. */
+int nerf_quantize_rgb8_gpu(nerf_ctx*, const float* rgb, int64_t n_pixels, int channels, uint8_t* out);
+
 /* Stage entry points (host buffers), one per reference function, used by the stage-wise parity tests. */
 int nerf_ray_dirs(nerf_ctx*, const nerf_camera*, int W, int H, int64_t ray_begin, int64_t ray_end,
                   float* dirs /*[n][3]*/);                                   /* lib.rs:214-230 + :371 */

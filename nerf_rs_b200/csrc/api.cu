@@ -65,6 +65,12 @@ struct nerf_ctx {
   std::recursive_mutex mu;
   DeviceNet nets[2];
   DevBuf dirs, tc, sigc, wc, tf, sigf, rgbf, out, in_a, in_b, jit, uni;
+  // 8-bit output path: two device frames + two pinned host frames so that the copy of one view overlaps the next render
+  DevBuf q8[2];
+  uint8_t* pinned[2] = {nullptr, nullptr};
+  size_t pinned_cap = 0;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_q[2] = {nullptr, nullptr}, ev_c[2] = {nullptr, nullptr};
   // timing
   struct Span { cudaEvent_t a, b; int kind; };
   std::vector<Span> spans;
@@ -167,6 +173,11 @@ int create_common(const TensorMap& coarse, const TensorMap& fine, int device, ne
   cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev_begin);
   if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev_end);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking);
+  for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+    e = cudaEventCreateWithFlags(&ctx->ev_q[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_c[i], cudaEventDisableTiming);
+  }
   if (e != cudaSuccess) {
     set_error(std::string("stream/event create: ") + cudaGetErrorString(e));
     delete ctx;
@@ -396,8 +407,15 @@ void nerf_destroy(nerf_ctx* c) {
     DeviceGuard g(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     for (DevBuf* b : {&c->dirs, &c->tc, &c->sigc, &c->wc, &c->tf, &c->sigf, &c->rgbf, &c->out, &c->in_a, &c->in_b,
-                      &c->jit, &c->uni})
+                      &c->jit, &c->uni, &c->q8[0], &c->q8[1]})
       b->release();
+    if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
+    for (int i = 0; i < 2; ++i) {
+      if (c->pinned[i]) cudaFreeHost(c->pinned[i]);
+      if (c->ev_q[i]) cudaEventDestroy(c->ev_q[i]);
+      if (c->ev_c[i]) cudaEventDestroy(c->ev_c[i]);
+    }
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     for (auto& n : c->nets) {
       if (n.blob) cudaFree(n.blob);
       for (auto& t : n.tc) free_tc_weights(&t);
@@ -549,6 +567,155 @@ int nerf_render_stages(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc
   static const nerf_stages none{};
   return render_host(c, cam, W, H, nc, nf, precision, smp, rb, re, rgb, st ? st : &none);
 }
+
+// ---------------------------------------------------------------------------- 8-bit output
+namespace nerf {
+namespace {
+int check_channels(int channels) {
+  if (channels != 3 && channels != 4) {
+    set_error("channels must be 3 (PPM body) or 4 (RGBA)");
+    return NERF_E_ARG;
+  }
+  return NERF_OK;
+}
+int reserve_pinned(nerf_ctx* c, size_t bytes) {
+  if (bytes <= c->pinned_cap) return NERF_OK;
+  for (int i = 0; i < 2; ++i) {
+    if (c->pinned[i]) cudaFreeHost(c->pinned[i]);
+    c->pinned[i] = nullptr;
+  }
+  c->pinned_cap = 0;
+  for (int i = 0; i < 2; ++i) NERF_CUDA(cudaMallocHost(reinterpret_cast<void**>(&c->pinned[i]), bytes));
+  c->pinned_cap = bytes;
+  return NERF_OK;
+}
+}  // namespace
+}  // namespace nerf
+
+int nerf_render_rgb8_device(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc, int nf, int precision,
+                            const nerf_sampling* smp, int64_t rb, int64_t re, int channels, uint8_t* d_out,
+                            void* stream) {
+  int rc = check_render_args(c, cam, W, H, nc, nf, smp, rb, re);
+  if (rc == NERF_OK) rc = check_channels(channels);
+  if (rc != NERF_OK) return rc;
+  if (re == rb) return NERF_OK;
+  if (!d_out) {
+    set_error("nerf_render_rgb8: null output");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  if ((rc = c->out.reserve((re - rb) * 12))) return rc;
+  const int mode = smp ? smp->mode : NERF_SAMPLING_DET;
+  timing_start(c, s);
+  rc = render_range(c, *cam, W, H, nc, nf, precision, mode, smp ? smp->seed : 0, smp ? smp->jitter : nullptr,
+                    smp ? smp->u : nullptr, rb, re, c->out.as<float>(), false, s);
+  if (rc == NERF_OK) {
+    NERF_CUDA(launch_quantize(c->out.as<float>(), re - rb, channels, d_out, s));
+    ++c->launches;
+  }
+  timing_stop(c, s);
+  return rc;
+}
+
+int nerf_render_rgb8(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc, int nf, int precision,
+                     const nerf_sampling* smp, int64_t rb, int64_t re, int channels, uint8_t* out) {
+  int rc = check_render_args(c, cam, W, H, nc, nf, smp, rb, re);
+  if (rc == NERF_OK) rc = check_channels(channels);
+  if (rc != NERF_OK) return rc;
+  const int64_t n = re - rb;
+  if (n == 0) return NERF_OK;
+  if (!out) {
+    set_error("nerf_render_rgb8: null output");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  cudaStream_t s = c->stream;
+  nerf_sampling dev = smp ? *smp : nerf_sampling{};
+  if (!smp) dev.mode = NERF_SAMPLING_DET;
+  if (dev.mode == NERF_SAMPLING_ARRAYS) {
+    if ((rc = c->jit.reserve(n * nc * 4)) || (rc = c->uni.reserve(std::max<int64_t>(n * nf, 1) * 4))) return rc;
+    NERF_CUDA(cudaMemcpyAsync(c->jit.p, smp->jitter, n * nc * 4, cudaMemcpyHostToDevice, s));
+    if (nf > 0) NERF_CUDA(cudaMemcpyAsync(c->uni.p, smp->u, n * nf * 4, cudaMemcpyHostToDevice, s));
+    dev.jitter = c->jit.as<float>();
+    dev.u = c->uni.as<float>();
+  }
+  const size_t bytes = (size_t)n * channels;
+  if ((rc = c->q8[0].reserve(bytes)) || (rc = reserve_pinned(c, bytes))) return rc;
+  rc = nerf_render_rgb8_device(c, cam, W, H, nc, nf, precision, &dev, rb, re, channels, c->q8[0].as<uint8_t>(), s);
+  if (rc != NERF_OK) return rc;
+  NERF_CUDA(cudaMemcpyAsync(c->pinned[0], c->q8[0].p, bytes, cudaMemcpyDeviceToHost, s));
+  NERF_CUDA(cudaStreamSynchronize(s));
+  std::memcpy(out, c->pinned[0], bytes);
+  return NERF_OK;
+}
+
+int nerf_render_many(nerf_ctx* c, const nerf_camera* cams, int n_views, int W, int H, int nc, int nf, int precision,
+                     const nerf_sampling* smp, int channels, uint8_t* out) {
+  if (!c || !cams || n_views < 0) {
+    set_error("nerf_render_many: null context or cameras");
+    return NERF_E_ARG;
+  }
+  if (smp && smp->mode == NERF_SAMPLING_ARRAYS) {
+    set_error("nerf_render_many: caller-supplied sample arrays are not supported");
+    return NERF_E_UNSUPPORTED;
+  }
+  const int64_t n = (int64_t)W * H;
+  int rc = check_channels(channels);
+  for (int v = 0; v < n_views && rc == NERF_OK; ++v) rc = check_render_args(c, &cams[v], W, H, nc, nf, smp, 0, n);
+  if (rc != NERF_OK) return rc;
+  if (n_views == 0) return NERF_OK;
+  if (!out) {
+    set_error("nerf_render_many: null output");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  const size_t bytes = (size_t)n * channels;
+  if ((rc = c->q8[0].reserve(bytes)) || (rc = c->q8[1].reserve(bytes)) || (rc = reserve_pinned(c, bytes))) return rc;
+  cudaStream_t s = c->stream;
+  auto drain = [&](int v) -> int {  // view v's bytes: pinned -> caller
+    NERF_CUDA(cudaEventSynchronize(c->ev_c[v & 1]));
+    std::memcpy(out + (size_t)v * bytes, c->pinned[v & 1], bytes);
+    return NERF_OK;
+  };
+  for (int v = 0; v < n_views; ++v) {
+    nerf_sampling sv = smp ? *smp : nerf_sampling{};
+    if (!smp) sv.mode = NERF_SAMPLING_DET;
+    sv.seed += (uint64_t)v;
+    // buffer v & 1 was last used by view v - 2, drained during iteration v - 1
+    rc = nerf_render_rgb8_device(c, &cams[v], W, H, nc, nf, precision, &sv, 0, n, channels, c->q8[v & 1].as<uint8_t>(), s);
+    if (rc != NERF_OK) return rc;
+    NERF_CUDA(cudaEventRecord(c->ev_q[v & 1], s));
+    NERF_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_q[v & 1], 0));
+    NERF_CUDA(cudaMemcpyAsync(c->pinned[v & 1], c->q8[v & 1].p, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+    NERF_CUDA(cudaEventRecord(c->ev_c[v & 1], c->copy_stream));
+    if (v > 0 && (rc = drain(v - 1))) return rc;  // overlaps view v's render
+  }
+  return drain(n_views - 1);
+}
+
+int nerf_quantize_rgb8_gpu(nerf_ctx* c, const float* rgb, int64_t n_pixels, int channels, uint8_t* out) {
+  if (!c || n_pixels < 0 || (n_pixels > 0 && (!rgb || !out))) {
+    set_error("nerf_quantize_rgb8_gpu: bad argument");
+    return NERF_E_ARG;
+  }
+  int rc = check_channels(channels);
+  if (rc != NERF_OK) return rc;
+  if (n_pixels == 0) return NERF_OK;
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  cudaStream_t s = c->stream;
+  if ((rc = c->out.reserve(n_pixels * 12)) || (rc = c->q8[0].reserve(n_pixels * channels))) return rc;
+  NERF_CUDA(cudaMemcpyAsync(c->out.p, rgb, n_pixels * 12, cudaMemcpyHostToDevice, s));
+  NERF_CUDA(launch_quantize(c->out.as<float>(), n_pixels, channels, c->q8[0].as<uint8_t>(), s));
+  NERF_CUDA(cudaMemcpyAsync(out, c->q8[0].p, n_pixels * channels, cudaMemcpyDeviceToHost, s));
+  NERF_CUDA(cudaStreamSynchronize(s));
+  return NERF_OK;
+}
+
 
 int nerf_ray_dirs(nerf_ctx* c, const nerf_camera* cam, int W, int H, int64_t rb, int64_t re, float* dirs) {
   if (!c || !cam || W <= 0 || H <= 0 || rb < 0 || re < rb || re > (int64_t)W * H || (!dirs && re > rb)) {

@@ -97,6 +97,7 @@ cudaError_t launch_importance(const float* d_tc, const float* d_sigc, const floa
                               float* d_wc_or_null, cudaStream_t s);
 cudaError_t launch_weights(const float* d_sigma, const float* d_t, int64_t n_rays, int n, float far_, float* d_w,
                            cudaStream_t s);
+cudaError_t launch_quantize(const float* d_rgb, int64_t n_pixels, int channels, uint8_t* d_out, cudaStream_t s);
 cudaError_t launch_composite(const float* d_rgb, const float* d_sigma, const float* d_t, int64_t n_rays, int n,
                              float far_, float* d_out, cudaStream_t s);
 

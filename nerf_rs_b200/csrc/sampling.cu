@@ -365,6 +365,32 @@ cudaError_t launch_weights(const float* d_sigma, const float* d_t, int64_t n_ray
   return cudaGetLastError();
 }
 
+// save_ppm / pixels_to_rgba quantiser (lib.rs:574-576, 586-589): (clamp(v, 0, 1) * 255 + 0.5) as u8.  Rust's `as u8`
+// truncates and saturates and maps NaN to 0; fmaxf(NaN, 0) = 0 gives the same.  Multiply and add round separately.
+__device__ __forceinline__ uint32_t quantize_one(float v) {
+  const float c = fminf(fmaxf(v, 0.0f), 1.0f);
+  return __float2uint_rz(__fadd_rn(__fmul_rn(c, 255.0f), 0.5f));
+}
+// One thread per pixel: 12 B in, 3 B (PPM body) or 4 B (RGBA, alpha 255) out.
+__global__ void quantize_kernel(const float* __restrict__ rgb, int64_t n_pixels, int channels, uint8_t* __restrict__ out) {
+  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pixels) return;
+  const uint32_t r = quantize_one(rgb[p * 3 + 0]), g = quantize_one(rgb[p * 3 + 1]), b = quantize_one(rgb[p * 3 + 2]);
+  if (channels == 4) {
+    reinterpret_cast<uint32_t*>(out)[p] = r | (g << 8) | (b << 16) | 0xff000000u;
+  } else {
+    out[p * 3 + 0] = (uint8_t)r;
+    out[p * 3 + 1] = (uint8_t)g;
+    out[p * 3 + 2] = (uint8_t)b;
+  }
+}
+
+cudaError_t launch_quantize(const float* d_rgb, int64_t n_pixels, int channels, uint8_t* d_out, cudaStream_t s) {
+  if (n_pixels == 0) return cudaSuccess;
+  quantize_kernel<<<(unsigned)((n_pixels + 255) / 256), 256, 0, s>>>(d_rgb, n_pixels, channels, d_out);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_composite(const float* d_rgb, const float* d_sigma, const float* d_t, int64_t n_rays, int n,
                              float far_, float* d_out, cudaStream_t s) {
   if (n_rays == 0) return cudaSuccess;

@@ -9,7 +9,7 @@ import ctypes as C
 
 import numpy as np
 
-from . import (DATA_ROOT, PRECISIONS, SAMPLING_ARRAYS, SAMPLING_DET, Sampling, Stages, Tensor, Timing, _check, _f32,
+from . import (Camera, DATA_ROOT, PRECISIONS, SAMPLING_ARRAYS, SAMPLING_DET, Sampling, Stages, Tensor, Timing, _check, _f32,
                _f32p, _p, lib)
 
 
@@ -129,6 +129,34 @@ class Renderer:
         smp = Sampling(mode=mode, seed=seed, jitter=d_jitter or None, u=d_u or None)
         _check(lib().nerf_render_device(self._h, C.byref(cam), W, H, n_coarse, n_fine, _prec(precision), C.byref(smp),
                                         ray_begin, ray_end, d_rgb, stream))
+
+    # ------------------------------------------------------------------ 8-bit output (save_ppm / pixels_to_rgba, lib.rs:567-592)
+    def render_rgb8(self, cam, W, H, n_coarse=64, n_fine=128, precision="fp16", mode=SAMPLING_DET, seed=0,
+                    jitter=None, u=None, ray_begin=0, ray_end=None, channels=3):
+        """render_image + the save_ppm quantiser on the device: uint8 [n, channels] (3 = PPM body, 4 = RGBA)."""
+        ray_end = W * H if ray_end is None else ray_end
+        out = np.empty((max(ray_end - ray_begin, 0), channels), np.uint8)
+        keep = []
+        smp = self._sampling(mode, seed, jitter, u, keep)
+        _check(lib().nerf_render_rgb8(self._h, C.byref(cam), W, H, n_coarse, n_fine, _prec(precision), C.byref(smp),
+                                      ray_begin, ray_end, channels, out.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return out
+
+    def render_many(self, cams, W, H, n_coarse=64, n_fine=128, precision="fp16", mode=SAMPLING_DET, seed=0, channels=3):
+        """A batch of poses: uint8 [n_views, H * W, channels]; copies overlap the next view's render."""
+        arr = (Camera * len(cams))(*cams)
+        out = np.empty((len(cams), W * H, channels), np.uint8)
+        smp = Sampling(mode=mode, seed=seed)
+        _check(lib().nerf_render_many(self._h, arr, len(cams), W, H, n_coarse, n_fine, _prec(precision), C.byref(smp),
+                                      channels, out.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return out
+
+    def quantize_rgb8_gpu(self, rgb, channels=3):
+        rgb = _f32(rgb).reshape(-1, 3)
+        out = np.empty((rgb.shape[0], channels), np.uint8)
+        _check(lib().nerf_quantize_rgb8_gpu(self._h, _p(rgb), rgb.shape[0], channels,
+                                            out.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return out
 
     # ------------------------------------------------------------------ stage entry points
     def ray_dirs(self, cam, W, H, ray_begin=0, ray_end=None):

@@ -8,6 +8,7 @@ import numpy as np
 import pytest
 
 from oracle import pyoracle as O
+import nerf_rs_b200 as nb
 
 pytestmark = pytest.mark.gpu
 
@@ -228,3 +229,64 @@ def test_cli_writes_the_same_ppm(renderer, cam, tmp_path):
     data = (tmp_path / "output.ppm").read_bytes()
     assert data.startswith(b"P6\n256 256\n255\n") and len(data) == 15 + 256 * 256 * 3
     assert "Rendering with 64 coarse samples and 128 fine samples per ray" in r.stdout
+
+
+# ---------------------------------------------------------------- 8-bit output on the device
+def test_quantiser_on_device_is_bit_exact(renderer):
+    """save_ppm's (clamp(v,0,1)*255+0.5) as u8 (lib.rs:574-576) on the GPU == the oracle, byte for byte, including
+    every rounding boundary k/255 +- 1 ulp, values outside [0,1], infinities and NaN (Rust: NaN as u8 == 0)."""
+    rng = np.random.default_rng(7)
+    edges = (np.arange(0, 256, dtype=np.float64)[:, None] + np.array([-0.5, 0.0, 0.5])[None, :]) / 255.0
+    edges = edges.astype(np.float32).ravel()
+    near = np.concatenate([np.nextafter(edges, np.float32(-1)), edges, np.nextafter(edges, np.float32(2))])
+    special = np.array([np.nan, -np.nan, np.inf, -np.inf, -0.0, 0.0, 1.0, 1.0000001, -1e-30, 1e30, 0.5, 255.0], np.float32)
+    v = np.concatenate([near, special, rng.uniform(-0.2, 1.2, 30000).astype(np.float32)])
+    v = np.resize(v, (v.size // 3 + 1) * 3).astype(np.float32)
+    want = O.quantize(v).reshape(-1, 3)
+    got3 = renderer.quantize_rgb8_gpu(v, channels=3)
+    assert (got3 == want).all()
+    got4 = renderer.quantize_rgb8_gpu(v, channels=4)  # pixels_to_rgba (lib.rs:582-592)
+    assert (got4[:, :3] == want).all() and (got4[:, 3] == 255).all()
+    assert renderer.quantize_rgb8_gpu(np.zeros((0, 3), np.float32)).shape == (0, 3)
+
+
+@pytest.mark.parametrize("channels", [3, 4])
+def test_render_rgb8_equals_quantised_float_frame(renderer, cam, channels):
+    W, H = 48, 32
+    img = renderer.render_image(cam, W, H, 64, 128, precision="fp16")
+    got = renderer.render_rgb8(cam, W, H, 64, 128, precision="fp16", channels=channels)
+    assert got.shape == (W * H, channels)
+    assert (got[:, :3] == O.quantize(img).reshape(-1, 3)).all()
+    if channels == 4:
+        assert (got[:, 3] == 255).all()
+    part = renderer.render_rgb8(cam, W, H, 64, 128, precision="fp16", channels=channels, ray_begin=100, ray_end=777)
+    assert (part == got[100:777]).all()
+    with pytest.raises(nb.NerfError):
+        renderer.render_rgb8(cam, W, H, 64, 128, channels=2)
+
+
+def test_render_many_equals_single_views(renderer, cam):
+    """A batch of poses (orbit sweep) returns, view by view, the bytes of the single-view call; Philox view v uses
+    seed + v."""
+    import copy
+    W, H = 40, 24
+    cams = []
+    for k in range(5):
+        c = copy.copy(cam)
+        a = 0.3 * k
+        o = np.array(cam.origin[:], np.float32)
+        rot = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]], np.float32)
+        c.origin[:] = (rot @ o).tolist()
+        c.forward[:] = (rot @ np.array(cam.forward[:], np.float32)).tolist()
+        c.up[:] = (rot @ np.array(cam.up[:], np.float32)).tolist()
+        cams.append(c)
+    many = renderer.render_many(cams, W, H, 16, 32, precision="fp16")
+    assert many.shape == (5, W * H, 3)
+    for k, c in enumerate(cams):
+        assert (many[k] == renderer.render_rgb8(c, W, H, 16, 32, precision="fp16")).all()
+    assert len({many[k].tobytes() for k in range(5)}) == 5  # the poses really differ
+    ph = renderer.render_many(cams[:3], W, H, 16, 32, precision="fp16", mode=nb.SAMPLING_PHILOX, seed=11, channels=4)
+    for k in range(3):
+        one = renderer.render_rgb8(cams[k], W, H, 16, 32, precision="fp16", mode=nb.SAMPLING_PHILOX, seed=11 + k, channels=4)
+        assert (ph[k] == one).all()
+    assert renderer.render_many([], W, H, 16, 32).shape == (0, W * H, 3)
