@@ -150,6 +150,16 @@ int nerf_render_many(nerf_ctx*, const nerf_camera* cams, int n_views, int W, int
 /* The quantiser alone on the device (host buffers): rgb [n_pixels][3] f32 -> out [n_pixels][channels]. */
 int nerf_quantize_rgb8_gpu(nerf_ctx*, const float* rgb, int64_t n_pixels, int channels, uint8_t* out);
 
+/* nerf_render plus two per-ray outputs the reference does not have (its integrate_ray, lib.rs:176-195, returns the
+ * colour only): depth = sum_i w_i * t_i and accumulated opacity acc = sum_i w_i over the weights of compute_weights
+ * (lib.rs:250-283), so that the background term of integrate_ray is 1 - acc.  depth / acc: [ray_end-ray_begin] f32,
+ * either may be null. */
+int nerf_render_aux(nerf_ctx*, const nerf_camera*, int W, int H, int n_coarse, int n_fine, int precision,
+                    const nerf_sampling*, int64_t ray_begin, int64_t ray_end, float* rgb, float* depth, float* acc);
+int nerf_render_aux_device(nerf_ctx*, const nerf_camera*, int W, int H, int n_coarse, int n_fine, int precision,
+                           const nerf_sampling*, int64_t ray_begin, int64_t ray_end, float* d_rgb, float* d_depth,
+                           float* d_acc, void* stream);
+
 /* Stage entry points (host buffers), one per reference function, used by the stage-wise parity tests. */
 int nerf_ray_dirs(nerf_ctx*, const nerf_camera*, int W, int H, int64_t ray_begin, int64_t ray_end,
                   float* dirs /*[n][3]*/);                                   /* lib.rs:214-230 + :371 */

@@ -31,7 +31,7 @@ EXPORTS = ["nerf_last_error", "nerf_version", "nerf_create", "nerf_create_from_t
            "nerf_render_stages", "nerf_ray_dirs", "nerf_compute_weights", "nerf_sample_importance",
            "nerf_integrate_rays", "nerf_get_timing", "nerf_camera_from_json", "nerf_camera_from_values",
            "nerf_save_ppm", "nerf_quantize_rgb8", "nerf_render_rgb8", "nerf_render_rgb8_device", "nerf_render_many",
-           "nerf_quantize_rgb8_gpu"]
+           "nerf_quantize_rgb8_gpu", "nerf_render_aux", "nerf_render_aux_device"]
 
 
 class NerfError(RuntimeError):
@@ -99,6 +99,8 @@ def lib():
     L.nerf_render_rgb8_device.argtypes = rargs + [i32, vp, vp]
     L.nerf_render_many.argtypes = [vp, C.POINTER(Camera), i32, i32, i32, i32, i32, i32, C.POINTER(Sampling), i32, u8p]
     L.nerf_quantize_rgb8_gpu.argtypes = [vp, _f32p, i64, i32, u8p]
+    L.nerf_render_aux.argtypes = rargs + [_f32p, _f32p, _f32p]
+    L.nerf_render_aux_device.argtypes = rargs + [vp, vp, vp, vp]
     L.nerf_ray_dirs.argtypes = [vp, C.POINTER(Camera), i32, i32, i64, i64, _f32p]
     L.nerf_compute_weights.argtypes = [vp, _f32p, _f32p, i64, i32, C.c_float, _f32p]
     L.nerf_sample_importance.argtypes = [vp, _f32p, _f32p, i64, i32, _f32p, i32, _f32p]

@@ -66,7 +66,7 @@ struct nerf_ctx {
   DeviceNet nets[2];
   DevBuf dirs, tc, sigc, wc, tf, sigf, rgbf, out, in_a, in_b, jit, uni;
   // 8-bit output path: two device frames + two pinned host frames so that the copy of one view overlaps the next render
-  DevBuf q8[2];
+  DevBuf q8[2], depth, acc;
   uint8_t* pinned[2] = {nullptr, nullptr};
   size_t pinned_cap = 0;
   cudaStream_t copy_stream = nullptr;
@@ -287,7 +287,7 @@ struct StagePtrs {  // device destinations for stage dumps (may be null)
 // MLP(fine) -> K4.  d_jit/d_u are device pointers indexed from ray rb.
 int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int nf, int precision, int mode,
                  uint64_t seed, const float* d_jit, const float* d_u, int64_t rb, int64_t re, float* d_rgb,
-                 bool want_wc, cudaStream_t s) {
+                 bool want_wc, cudaStream_t s, float* d_depth = nullptr, float* d_acc = nullptr) {
   const RayBasis basis = make_basis(cam, W, H);
   const int nm = nc + nf;
   for (int64_t b0 = rb; b0 < re; b0 += c->chunk_rays) {
@@ -335,7 +335,7 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
 
     span_begin(c, ST_COMPOSITE, s);
     NERF_CUDA(launch_composite(c->rgbf.as<float>(), c->sigf.as<float>(), c->tf.as<float>(), n, nm, cam.far_,
-                               d_rgb + off * 3, s));
+                               d_rgb + off * 3, d_depth ? d_depth + off : nullptr, d_acc ? d_acc + off : nullptr, s));
     span_end(c, s);
     ++c->launches;
   }
@@ -407,7 +407,7 @@ void nerf_destroy(nerf_ctx* c) {
     DeviceGuard g(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     for (DevBuf* b : {&c->dirs, &c->tc, &c->sigc, &c->wc, &c->tf, &c->sigf, &c->rgbf, &c->out, &c->in_a, &c->in_b,
-                      &c->jit, &c->uni, &c->q8[0], &c->q8[1]})
+                      &c->jit, &c->uni, &c->q8[0], &c->q8[1], &c->depth, &c->acc})
       b->release();
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
     for (int i = 0; i < 2; ++i) {
@@ -717,6 +717,61 @@ int nerf_quantize_rgb8_gpu(nerf_ctx* c, const float* rgb, int64_t n_pixels, int 
 }
 
 
+// ---------------------------------------------------------------------------- depth / opacity
+int nerf_render_aux_device(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc, int nf, int precision,
+                           const nerf_sampling* smp, int64_t rb, int64_t re, float* d_rgb, float* d_depth,
+                           float* d_acc, void* stream) {
+  int rc = check_render_args(c, cam, W, H, nc, nf, smp, rb, re);
+  if (rc != NERF_OK) return rc;
+  if (re == rb) return NERF_OK;
+  if (!d_rgb) {
+    set_error("nerf_render_aux: null rgb output");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int mode = smp ? smp->mode : NERF_SAMPLING_DET;
+  timing_start(c, s);
+  rc = render_range(c, *cam, W, H, nc, nf, precision, mode, smp ? smp->seed : 0, smp ? smp->jitter : nullptr,
+                    smp ? smp->u : nullptr, rb, re, d_rgb, false, s, d_depth, d_acc);
+  timing_stop(c, s);
+  return rc;
+}
+
+int nerf_render_aux(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc, int nf, int precision,
+                    const nerf_sampling* smp, int64_t rb, int64_t re, float* rgb, float* depth, float* acc) {
+  int rc = check_render_args(c, cam, W, H, nc, nf, smp, rb, re);
+  if (rc != NERF_OK) return rc;
+  const int64_t n = re - rb;
+  if (n == 0) return NERF_OK;
+  if (!rgb) {
+    set_error("nerf_render_aux: null rgb output");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  cudaStream_t s = c->stream;
+  nerf_sampling dev = smp ? *smp : nerf_sampling{};
+  if (!smp) dev.mode = NERF_SAMPLING_DET;
+  if (dev.mode == NERF_SAMPLING_ARRAYS) {
+    if ((rc = c->jit.reserve(n * nc * 4)) || (rc = c->uni.reserve(std::max<int64_t>(n * nf, 1) * 4))) return rc;
+    NERF_CUDA(cudaMemcpyAsync(c->jit.p, smp->jitter, n * nc * 4, cudaMemcpyHostToDevice, s));
+    if (nf > 0) NERF_CUDA(cudaMemcpyAsync(c->uni.p, smp->u, n * nf * 4, cudaMemcpyHostToDevice, s));
+    dev.jitter = c->jit.as<float>();
+    dev.u = c->uni.as<float>();
+  }
+  if ((rc = c->out.reserve(n * 12)) || (rc = c->depth.reserve(n * 4)) || (rc = c->acc.reserve(n * 4))) return rc;
+  rc = nerf_render_aux_device(c, cam, W, H, nc, nf, precision, &dev, rb, re, c->out.as<float>(),
+                              depth ? c->depth.as<float>() : nullptr, acc ? c->acc.as<float>() : nullptr, s);
+  if (rc != NERF_OK) return rc;
+  NERF_CUDA(cudaMemcpyAsync(rgb, c->out.p, n * 12, cudaMemcpyDeviceToHost, s));
+  if (depth) NERF_CUDA(cudaMemcpyAsync(depth, c->depth.p, n * 4, cudaMemcpyDeviceToHost, s));
+  if (acc) NERF_CUDA(cudaMemcpyAsync(acc, c->acc.p, n * 4, cudaMemcpyDeviceToHost, s));
+  NERF_CUDA(cudaStreamSynchronize(s));
+  return NERF_OK;
+}
+
 int nerf_ray_dirs(nerf_ctx* c, const nerf_camera* cam, int W, int H, int64_t rb, int64_t re, float* dirs) {
   if (!c || !cam || W <= 0 || H <= 0 || rb < 0 || re < rb || re > (int64_t)W * H || (!dirs && re > rb)) {
     set_error("nerf_ray_dirs: bad argument");
@@ -800,7 +855,7 @@ int nerf_integrate_rays(nerf_ctx* c, const float* rgb, const float* sigma, const
     NERF_CUDA(cudaMemcpyAsync(c->tf.p, t, n_rays * n * 4, cudaMemcpyHostToDevice, c->stream));
   }
   NERF_CUDA(launch_composite(c->rgbf.as<float>(), c->sigf.as<float>(), c->tf.as<float>(), n_rays, n, far_,
-                             c->out.as<float>(), c->stream));
+                             c->out.as<float>(), nullptr, nullptr, c->stream));
   NERF_CUDA(cudaMemcpyAsync(out, c->out.p, n_rays * 12, cudaMemcpyDeviceToHost, c->stream));
   NERF_CUDA(cudaStreamSynchronize(c->stream));
   return NERF_OK;

@@ -99,6 +99,7 @@ cudaError_t launch_weights(const float* d_sigma, const float* d_t, int64_t n_ray
                            cudaStream_t s);
 cudaError_t launch_quantize(const float* d_rgb, int64_t n_pixels, int channels, uint8_t* d_out, cudaStream_t s);
 cudaError_t launch_composite(const float* d_rgb, const float* d_sigma, const float* d_t, int64_t n_rays, int n,
-                             float far_, float* d_out, cudaStream_t s);
+                             float far_, float* d_out, float* d_depth /*nullable*/, float* d_acc /*nullable*/,
+                             cudaStream_t s);
 
 }  // namespace nerf

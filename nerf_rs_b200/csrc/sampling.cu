@@ -282,26 +282,30 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) weights_kernel(const float*
 __global__ void __launch_bounds__(kWarpsPerCta * 32) composite_kernel(const float* __restrict__ rgb,
                                                                       const float* __restrict__ sigma,
                                                                       const float* __restrict__ t, int64_t n_rays,
-                                                                      int n, float far_, float* __restrict__ out) {
+                                                                      int n, float far_, float* __restrict__ out,
+                                                                      float* __restrict__ depth_out,
+                                                                      float* __restrict__ acc_out) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int64_t ray = blockIdx.x * (int64_t)kWarpsPerCta + warp; ray < n_rays; ray += (int64_t)gridDim.x * kWarpsPerCta) {
     const float* sr = sigma + ray * n;
     const float* tr = t + ray * n;
     const float* cr = rgb + ray * n * 3;
-    float r = 0.0f, g = 0.0f, b = 0.0f, acc = 0.0f, carry = 1.0f;
+    float r = 0.0f, g = 0.0f, b = 0.0f, acc = 0.0f, depth = 0.0f, carry = 1.0f;
     for (int base = 0; base < n; base += 32) {
       const int i = base + lane;
-      float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f;
+      float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f, ti = 0.0f;
       if (i < n) {
         c0 = cr[i * 3 + 0];
         c1 = cr[i * 3 + 1];
         c2 = cr[i * 3 + 2];
+        ti = tr[i];
       }
       const float wi = warp_weights_round(sr, tr, n, far_, base, lane, carry);
       r += c0 * wi;
       g += c1 * wi;
       b += c2 * wi;
       acc += wi;
+      depth += wi * ti;
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
@@ -309,7 +313,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) composite_kernel(const floa
       g += __shfl_xor_sync(kFull, g, d);
       b += __shfl_xor_sync(kFull, b, d);
       acc += __shfl_xor_sync(kFull, acc, d);
+      depth += __shfl_xor_sync(kFull, depth, d);
     }
+    // optional outputs the reference does not have: depth = sum w_i t_i, accumulated opacity = sum w_i
+    if (lane == 0 && depth_out != nullptr) depth_out[ray] = depth;
+    if (lane == 0 && acc_out != nullptr) acc_out[ray] = acc;
     if (n == 0) { r = g = b = 0.0f; acc = 1.0f; }  // lib.rs:178-180: no samples -> black
     const float bg = 1.0f - acc;                   // lib.rs:194
     const float v = lane == 0 ? r + bg : (lane == 1 ? g + bg : b + bg);
@@ -392,10 +400,10 @@ cudaError_t launch_quantize(const float* d_rgb, int64_t n_pixels, int channels, 
 }
 
 cudaError_t launch_composite(const float* d_rgb, const float* d_sigma, const float* d_t, int64_t n_rays, int n,
-                             float far_, float* d_out, cudaStream_t s) {
+                             float far_, float* d_out, float* d_depth, float* d_acc, cudaStream_t s) {
   if (n_rays == 0) return cudaSuccess;
   composite_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, 0, s>>>(d_rgb, d_sigma, d_t, n_rays, n, far_,
-                                                                                d_out);
+                                                                                d_out, d_depth, d_acc);
   return cudaGetLastError();
 }
 

@@ -151,6 +151,18 @@ class Renderer:
                                       channels, out.ctypes.data_as(C.POINTER(C.c_uint8))))
         return out
 
+    def render_aux(self, cam, W, H, n_coarse=64, n_fine=128, precision="fp16", mode=SAMPLING_DET, seed=0,
+                   jitter=None, u=None, ray_begin=0, ray_end=None):
+        """render_image plus depth (sum w_i t_i) and accumulated opacity (sum w_i): (rgb [n,3], depth [n], acc [n])."""
+        ray_end = W * H if ray_end is None else ray_end
+        n = max(ray_end - ray_begin, 0)
+        rgb, depth, acc = np.empty((n, 3), np.float32), np.empty(n, np.float32), np.empty(n, np.float32)
+        keep = []
+        smp = self._sampling(mode, seed, jitter, u, keep)
+        _check(lib().nerf_render_aux(self._h, C.byref(cam), W, H, n_coarse, n_fine, _prec(precision), C.byref(smp),
+                                     ray_begin, ray_end, _p(rgb), _p(depth), _p(acc)))
+        return rgb, depth, acc
+
     def quantize_rgb8_gpu(self, rgb, channels=3):
         rgb = _f32(rgb).reshape(-1, 3)
         out = np.empty((rgb.shape[0], channels), np.uint8)

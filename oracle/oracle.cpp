@@ -462,6 +462,23 @@ int oracle_sample_importance(const float* t, const float* w, int n, const float*
   return count;
 }
 
+// Depth and accumulated opacity of a ray.  The reference has neither output; the definition used here is the usual
+// one over the weights of compute_weights (lib.rs:250-283) that integrate_ray (lib.rs:176-195) also uses:
+// acc = sum_i w_i (so that integrate_ray's background term is 1 - acc), depth = sum_i w_i * t_i, f32, ascending i.
+void oracle_integrate_aux(const float* sigma, const float* t, int n, float far_, float out[2]) {
+  out[0] = out[1] = 0.0f;
+  if (n == 0) return;
+  std::vector<float> w(n);
+  oracle_compute_weights(sigma, t, n, far_, w.data());
+  float depth = 0.0f, acc = 0.0f;
+  for (int i = 0; i < n; ++i) {
+    depth += w[i] * t[i];
+    acc += w[i];
+  }
+  out[0] = depth;
+  out[1] = acc;
+}
+
 // integrate_ray (lib.rs:176-195).
 void oracle_integrate_ray(const float* rgb, const float* sigma, const float* t, int n, float far_, float out[3]) {
   if (n == 0) {

@@ -79,6 +79,8 @@ void oracle_stratified(float near_, float far_, int count, const float* jitter, 
 void oracle_compute_weights(const float* sigma, const float* t, int n, float far_, float* w_out);
 /* returns number of samples written (0 or count) */
 int oracle_sample_importance(const float* t, const float* w, int n, const float* u, int count, float* out);
+/* depth = sum w_i t_i, acc = sum w_i over compute_weights' weights (no reference counterpart; see oracle.cpp) */
+void oracle_integrate_aux(const float* sigma, const float* t, int n, float far_, float out[2]);
 void oracle_integrate_ray(const float* rgb /*[n][3]*/, const float* sigma, const float* t, int n, float far_,
                           float out[3]);
 /* Uniforms shared bit-for-bit with the CUDA path: Philox4x32-10, key=(seed lo,hi),

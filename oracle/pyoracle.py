@@ -61,6 +61,7 @@ def lib():
     L.oracle_compute_weights.argtypes = [_f32p, _f32p, C.c_int, C.c_float, _f32p]
     L.oracle_sample_importance.argtypes = [_f32p, _f32p, C.c_int, _f32p, C.c_int, _f32p]
     L.oracle_integrate_ray.argtypes = [_f32p, _f32p, _f32p, C.c_int, C.c_float, _f32p]
+    L.oracle_integrate_aux.argtypes = [_f32p, _f32p, C.c_int, C.c_float, _f32p]
     L.oracle_philox_uniforms.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_int, _f32p]
     L.oracle_render.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_int,
                                 C.POINTER(Sampling), C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, _f32p,
@@ -161,6 +162,14 @@ def sample_importance(t, w, u):
     out = np.empty(len(u), np.float32)
     n = lib().oracle_sample_importance(_p(t), _p(w), len(t), _p(u), len(u), _p(out))
     return out[:n]
+
+
+def integrate_aux(sigma, t, far):
+    """(depth, acc) = (sum w_i t_i, sum w_i) over compute_weights' weights."""
+    sigma, t = _f32(sigma), _f32(t)
+    out = np.empty(2, np.float32)
+    lib().oracle_integrate_aux(_p(sigma), _p(t), len(t), far, _p(out))
+    return out
 
 
 def integrate_ray(rgb, sigma, t, far):

@@ -290,3 +290,25 @@ def test_render_many_equals_single_views(renderer, cam):
         one = renderer.render_rgb8(cams[k], W, H, 16, 32, precision="fp16", mode=nb.SAMPLING_PHILOX, seed=11 + k, channels=4)
         assert (ph[k] == one).all()
     assert renderer.render_many([], W, H, 16, 32).shape == (0, W * H, 3)
+
+
+# ---------------------------------------------------------------- depth / accumulated opacity
+def test_render_aux_depth_and_opacity(renderer, cam):
+    """depth = sum w_i t_i and acc = sum w_i (oracle.cpp::oracle_integrate_aux; the reference has neither) on the
+    GPU's own fine samples; rgb is unchanged by asking for them, and 1 - acc is integrate_ray's background term."""
+    W, H, nc, nf = 24, 16, 16, 32
+    rgb0, st = renderer.render_image(cam, W, H, nc, nf, precision="fp32", stages=True)
+    rgb, depth, acc = renderer.render_aux(cam, W, H, nc, nf, precision="fp32")
+    assert (rgb == rgb0).all()
+    want = np.stack([O.integrate_aux(st["sigma_f"][r], st["t_f"][r], cam.far) for r in range(W * H)])
+    assert np.abs(depth - want[:, 0]).max() <= 2e-5 * cam.far
+    assert np.abs(acc - want[:, 1]).max() <= 2e-6
+    assert (acc >= 0).all() and (acc <= 1 + 1e-6).all() and (depth >= 0).all() and (depth <= cam.far * (1 + 1e-6)).all()
+    hit = acc > 0.5
+    assert hit.any() and (~hit).any()  # the frame contains both object and background
+    assert (depth[hit] / acc[hit] > cam.near).all() and (depth[hit] / acc[hit] < cam.far).all()
+    colour = np.einsum("rnc,rn->rc", st["rgb_f"].astype(np.float64),
+                       np.stack([O.compute_weights(st["sigma_f"][r], st["t_f"][r], cam.far) for r in range(W * H)]))
+    assert np.abs(rgb - (colour + (1.0 - acc[:, None]))).max() < 1e-5
+    part = renderer.render_aux(cam, W, H, nc, nf, precision="fp32", ray_begin=50, ray_end=200)
+    assert (part[1] == depth[50:200]).all() and (part[2] == acc[50:200]).all()

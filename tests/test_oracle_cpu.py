@@ -208,3 +208,18 @@ def test_cli_builds_and_fails_loudly_without_gpu(tmp_path):
         pass
     r = subprocess.run([cli, "--weights", DATA, "--out", str(tmp_path / "o.ppm")], capture_output=True, text=True)
     assert r.returncode != 0 and "no CPU fallback" in r.stderr and not (tmp_path / "o.ppm").exists()
+
+
+def test_integrate_aux_closed_form():
+    """Constant sigma on a uniform grid: T_i = exp(-sigma * i * d), acc = 1 - exp(-sigma * L) up to the T < 1e-4
+    cut-off of compute_weights (lib.rs:276-279), depth = sum w_i t_i by direct summation."""
+    n, sigma, near, far = 64, 0.7, 2.0, 6.0
+    t = (near + (far - near) * np.arange(n) / n).astype(np.float32)
+    s = np.full(n, sigma, np.float32)
+    depth, acc = O.integrate_aux(s, t, far)
+    w = O.compute_weights(s, t, far).astype(np.float64)
+    assert abs(acc - w.sum()) < 1e-6 and abs(depth - (w * t).sum()) < 1e-5
+    assert abs(acc - (1.0 - np.exp(-sigma * (far - near)))) < 2e-4
+    assert tuple(O.integrate_aux(np.zeros(0, np.float32), np.zeros(0, np.float32), far)) == (0.0, 0.0)
+    d0, a0 = O.integrate_aux(np.zeros(n, np.float32), t, far)  # empty space
+    assert d0 == 0.0 and a0 == 0.0
