@@ -57,6 +57,7 @@ constexpr uint32_t kBarFull = 0, kBarPFull = 32, kBarEmpty = 64, kBarAcc = 96, k
 constexpr uint32_t kSmemBytes = kOffBar + 256;  // 224.25 KiB
 static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 constexpr int kLead = 4;  // chunks of a layer slot X issues before slot Y starts the same layer
+constexpr int kEpiRegs = 112, kCtlRegs = 32;  // 512 * 112 + 128 * 32 = 61440 <= 65536 registers per SM
 
 // Layer table: chunks per layer in consumption order.
 constexpr int kNumLayers = 10;  // dense0..7, bottleneck, viewdirs
@@ -356,6 +357,14 @@ __device__ __forceinline__ void write_pe16(uint8_t* aux_row, uint32_t r8, const 
     *reinterpret_cast<uint4*>(aux_row + ((((uint32_t)(kCol0 / 8 + h)) ^ r8) << 4)) = q;
   }
 }
+// Register rebalancing (setmaxnreg): the launch gives each of the 640 threads 96 registers; the control warp group
+// (warps 16..19) shrinks to kCtlRegs and the four epilogue warp groups grow to kEpiRegs, which is what the epilogue
+// needs to keep two 32-column accumulator blocks plus the prefetched inputs in registers.  A spill here is an L2
+// round trip (227 KB of the SM's array is shared memory, so local memory does not stay in L1).  Each role's branch
+// executes its own instruction: ptxas takes a region's register limit from the setmaxnreg that dominates it, and
+// after a merge of branches with different limits it assumes the smallest.
+__device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kCtlRegs)); }
+__device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kEpiRegs)); }
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
@@ -413,6 +422,7 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
   for (int l = 0; l < n_layers; ++l) n_chunks_quad += layer_chunks(l);
 
   if (warp == kWarpTma) {
+    reg_dec();
     // ===================================================== TMA producer: this CTA's half of every weight chunk
     Tracer tr{(trace != nullptr && blockIdx.x == 0 && lane == 0) ? trace + 1 * 2 * kTraceCap : nullptr, 0};
     uint32_t stage = 0, phase = 0;
@@ -437,7 +447,10 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
         }
       }
     }
+  } else if (warp == kWarpAlloc) {
+    reg_dec();  // all four warps of the group must execute it
   } else if (warp == kWarpRelay) {
+    reg_dec();
     // ===================================================== relay: tell the leader that this CTA's half has landed
     Tracer tr{(trace != nullptr && blockIdx.x == 0 && lane == 0) ? trace + 6 * 2 * kTraceCap : nullptr, 0};
     uint32_t stage = 0, phase = 0;
@@ -455,6 +468,7 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
       }
     }
   } else if (warp == kWarpMma) {
+    reg_dec();
     // ===================================================== MMA issuer (leader CTA): one thread drives both tensor cores
     if (rank == 0) {
       Tracer tr{(trace != nullptr && blockIdx.x == 0 && lane == 0) ? trace : nullptr, 0};
@@ -528,6 +542,7 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
       }
     }
   } else if (warp < kEpiWarps) {
+    reg_inc();
     // ===================================================== epilogue warps: one thread per (sample row, column quarter)
     const int colq = warp >> 2;
     const uint32_t quad = (uint32_t)(warp & 3);
