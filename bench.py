@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark: lego 800x800, 64 coarse + 128 fine samples/ray, rays/s.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--precision fp16|bf16|fp32] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--precision fp16|bf16|fp16x3|fp32] [--impl reference]
 
 A step = one full 800x800 frame (640 000 rays, 163.84 M MLP samples) through the whole hot path
 (ray gen -> stratified -> coarse MLP -> importance resampling -> fine MLP -> compositing).
@@ -259,12 +259,14 @@ def gpu_arm(args):
             "e2e_many": None if many_ms is None else {
                 "value": 4 * n_rays / (many_ms * 1e-3), "unit": "rays/s", "views": 4,
                 "api": "nerf_render_many (pinned double buffer, copies overlap the next view)"},
-            "roofline": {"bound": "tensor", "kernel": "mlp_tc_kernel (fine pass)", "achieved": ach, "peak": sustained,
+            "roofline": {"bound": "tensor", "kernel": {"fp16x3": "mlp_tc_x3_kernel (fine pass; 3 MMAs per product, credited once)",
+                                                       "fp32": "mlp_fp32_kernel (fine pass; CUDA cores)"}.get(
+                             args.precision, "mlp_tc_kernel (fine pass)"), "achieved": ach, "peak": sustained,
                          "unit": "TFLOP/s", "frac": ach / sustained, "peak_kind": f"bf16 sustained, {kind}",
                          "frac_of_burst": ach / burst,
                          # DRAM bytes of the fine-pass launch of one full frame (ncu --set full, read + write,
                          # profiles/r01_mlp_tc_v15_ncu_full_summary.csv), scaled to this rank's share of the rays
-                         "traffic": NCU_FINE_DRAM_GB * n_local / n_rays, "traffic_unit": "GB per launch (ncu dram read+write)"},
+                         "traffic": NCU_FINE_DRAM_GB * n_local / n_rays if args.precision in ("fp16", "bf16") else None, "traffic_unit": "GB per launch (ncu dram read+write)"},
         }
         if world == 1 and not args.no_cpu:
             O, ctx, cores, begin, n = cpu_sample()
@@ -284,7 +286,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--precision", default="fp16", choices=["fp16", "bf16", "fp32"])
+    ap.add_argument("--precision", default="fp16", choices=["fp16", "bf16", "fp16x3", "fp32"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()

@@ -42,7 +42,10 @@ typedef enum {
   NERF_PREC_FP32 = 0, /* CUDA-core path; per-element sum order identical to network.rs:134-143 */
   NERF_PREC_BF16 = 1, /* tcgen05 kind::f16, bf16 operands, f32 accumulate in TMEM */
   NERF_PREC_FP16 = 2, /* tcgen05 kind::f16, fp16 operands (tf32-class 10-bit mantissa at bf16 rate) */
-  NERF_PREC_TF32 = 3  /* reserved; currently served by the FP16 path (same operand mantissa) */
+  NERF_PREC_TF32 = 3, /* served by the FP16 path (same 10-bit operand mantissa at twice the tf32 rate) */
+  NERF_PREC_FP16X3 = 4 /* tcgen05 kind::f16, every operand split x = hi + lo (two fp16), three MMAs per product
+                        * (hi.hi + lo.hi + hi.lo), f32 accumulate: ~22-bit operands, f32-class results at a third
+                        * of the FP16 rate.  The mode that meets the reference-accuracy bounds on the tensor cores. */
 } nerf_precision;
 
 typedef enum { NERF_NET_COARSE = 0, NERF_NET_FINE = 1 } nerf_net_id;

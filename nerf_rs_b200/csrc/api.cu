@@ -49,6 +49,7 @@ struct DeviceNet {
   float* blob = nullptr;  // every f32 tensor of the network, file layout, 16-byte aligned segments
   NetF32 f32{};
   TcWeights tc[2];        // [0] bf16, [1] fp16 pre-swizzled operand tiles (mlp_tc.cu)
+  TcWeights tcx3;         // fp16 hi / lo split tiles of the fp16x3 mode (mlp_tc_x3.cu)
 };
 
 enum StageKind { ST_SAMPLING = 0, ST_MLP_COARSE, ST_MLP_FINE, ST_COMPOSITE, ST_COUNT };
@@ -134,7 +135,7 @@ int upload_network(const TensorMap& t, DeviceNet* net) {
     int rc = build_tc_weights(t, fmt, net->f32, &net->tc[fmt]);
     if (rc != NERF_OK) return rc;
   }
-  return NERF_OK;
+  return build_tc_x3_weights(t, &net->tcx3);
 }
 
 int create_common(const TensorMap& coarse, const TensorMap& fine, int device, nerf_ctx** out) {
@@ -240,6 +241,9 @@ int run_mlp(nerf_ctx* c, int net, const SampleSrc& src, const SampleDst& dst, in
     case NERF_PREC_FP16:
     case NERF_PREC_TF32:
       e = launch_mlp_tc(c->nets[net].tc[1], src, dst, c->sm_count, s);
+      break;
+    case NERF_PREC_FP16X3:
+      e = launch_mlp_tc_x3(c->nets[net].tcx3, src, dst, c->sm_count, s);
       break;
     default:
       set_error("unknown precision");
@@ -419,6 +423,7 @@ void nerf_destroy(nerf_ctx* c) {
     for (auto& n : c->nets) {
       if (n.blob) cudaFree(n.blob);
       for (auto& t : n.tc) free_tc_weights(&t);
+      free_tc_weights(&n.tcx3);
     }
     for (auto& sp : c->spans) {
       cudaEventDestroy(sp.a);

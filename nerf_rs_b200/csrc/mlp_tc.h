@@ -21,7 +21,7 @@ struct alignas(16) TcConsts {
 struct TcWeights {
   uint8_t* d_chunks = nullptr;
   size_t bytes = 0;
-  int fmt = 0;  // 0 = bf16, 1 = fp16
+  int fmt = 0;  // 0 = bf16, 1 = fp16, 2 = fp16 hi/lo split (fp16x3)
   TcConsts consts;
 };
 
@@ -29,5 +29,10 @@ int build_tc_weights(const TensorMap& t, int fmt, const NetF32& f32, TcWeights* 
 void free_tc_weights(TcWeights* w);
 cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
                           cudaStream_t s);
+
+// fp16x3 mode (mlp_tc_x3.cu): every weight K-block as a hi and a lo fp16 chunk (fmt = 2), three MMAs per product.
+int build_tc_x3_weights(const TensorMap& t, TcWeights* out);
+cudaError_t launch_mlp_tc_x3(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
+                             cudaStream_t s);
 
 }  // namespace nerf
