@@ -46,6 +46,12 @@ typedef enum {
   NERF_PREC_FP16X3 = 4 /* tcgen05 kind::f16, every operand split x = hi + lo (two fp16), three MMAs per product
                         * (hi.hi + lo.hi + hi.lo), f32 accumulate: ~22-bit operands, f32-class results at a third
                         * of the FP16 rate.  The mode that meets the reference-accuracy bounds on the tensor cores. */
+  ,
+  NERF_PREC_MIXED = 5  /* coarse network FP16X3, fine network FP16.  The coarse densities only place the fine samples
+                        * (lib.rs:409-420), and where the coarse weights are almost zero the inverse CDF turns a 1e-4
+                        * weight error into a visible shift of a sample; on thin structures that is the whole
+                        * difference between an FP16 frame and the f32 one.  With f32-class coarse densities the
+                        * frame stays within 2/255 of the f32 frame at 2/3 of the FP16 frame rate. */
 } nerf_precision;
 
 typedef enum { NERF_NET_COARSE = 0, NERF_NET_FINE = 1 } nerf_net_id;

@@ -245,6 +245,10 @@ int run_mlp(nerf_ctx* c, int net, const SampleSrc& src, const SampleDst& dst, in
     case NERF_PREC_FP16X3:
       e = launch_mlp_tc_x3(c->nets[net].tcx3, src, dst, c->sm_count, s);
       break;
+    case NERF_PREC_MIXED:  // coarse network at f32-class accuracy (it places the fine samples), fine network in fp16
+      e = net == NERF_NET_COARSE ? launch_mlp_tc_x3(c->nets[net].tcx3, src, dst, c->sm_count, s)
+                                 : launch_mlp_tc(c->nets[net].tc[1], src, dst, c->sm_count, s);
+      break;
     default:
       set_error("unknown precision");
       return NERF_E_ARG;

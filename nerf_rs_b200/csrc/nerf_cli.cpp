@@ -21,7 +21,7 @@ namespace {
 void usage() {
   std::printf(
       "usage: nerf_cli [--weights DIR] [--camera JSON] [--width W] [--height H] [--nc N] [--nf N]\n"
-      "                [--precision fp32|bf16|fp16|tf32|fp16x3] [--det | --seed S] [--device D] [--out FILE]\n"
+      "                [--precision fp32|bf16|fp16|tf32|fp16x3|mixed] [--det | --seed S] [--device D] [--out FILE]\n"
       "defaults reproduce the reference CLI: 256x256, 64 coarse + 128 fine samples, output.ppm\n");
 }
 
@@ -35,7 +35,7 @@ int fail(const char* what) {
 int main(int argc, char** argv) {
   std::string root = "lego_rust", cam_path, out = "output.ppm";
   if (const char* e = std::getenv("NERF_B200_WEIGHTS")) root = e;
-  int W = 256, H = 256, nc = 64, nf = 128, precision = NERF_PREC_FP16, device = 0;
+  int W = 256, H = 256, nc = 64, nf = 128, precision = NERF_PREC_MIXED, device = 0;
   nerf_sampling smp{};
   smp.mode = NERF_SAMPLING_PHILOX;
   smp.seed = 0;
@@ -65,6 +65,7 @@ int main(int argc, char** argv) {
       else if (p == "fp16") precision = NERF_PREC_FP16;
       else if (p == "tf32") precision = NERF_PREC_TF32;
       else if (p == "fp16x3") precision = NERF_PREC_FP16X3;
+      else if (p == "mixed") precision = NERF_PREC_MIXED;
       else { std::fprintf(stderr, "nerf_cli: unknown precision %s\n", p.c_str()); return 2; }
     } else if (a == "--help" || a == "-h") { usage(); return 0; }
     else { std::fprintf(stderr, "nerf_cli: unknown argument %s\n", a.c_str()); usage(); return 2; }

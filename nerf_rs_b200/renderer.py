@@ -24,7 +24,7 @@ class Network:
         self._r = renderer
         self.net_id = net_id
 
-    def forward_batch(self, points, view_dirs, precision="fp16"):
+    def forward_batch(self, points, view_dirs, precision="mixed"):
         """points: [3, B] feature-major (the reference's Matrix 3xB); view_dirs: [B, 3].
 
         Returns (rgb [B, 3], sigma [B]).  An empty batch returns empty arrays (network.rs:199-201)."""
@@ -41,7 +41,7 @@ class Network:
                                         _p(rgb), _p(sigma)))
         return rgb, sigma
 
-    def forward_batch_device(self, d_points, d_dirs, B, d_rgb, d_sigma, precision="fp16", stream=0):
+    def forward_batch_device(self, d_points, d_dirs, B, d_rgb, d_sigma, precision="mixed", stream=0):
         """Same on device pointers (ints), enqueued on `stream` without synchronising."""
         _check(lib().nerf_forward_batch_device(self._r._h, self.net_id, d_points, d_dirs, B, _prec(precision), d_rgb,
                                                d_sigma, stream))
@@ -100,7 +100,7 @@ class Renderer:
                 s.jitter, s.u = jitter.ctypes.data, u.ctypes.data
         return s
 
-    def render_image(self, cam, W, H, n_coarse=64, n_fine=128, precision="fp16", mode=SAMPLING_DET, seed=0,
+    def render_image(self, cam, W, H, n_coarse=64, n_fine=128, precision="mixed", mode=SAMPLING_DET, seed=0,
                      jitter=None, u=None, ray_begin=0, ray_end=None, stages=False, out=None):
         """Returns rgb [n, 3] for pixel indices [ray_begin, ray_end) (and the stage dict when stages=True)."""
         ray_end = W * H if ray_end is None else ray_end
@@ -122,7 +122,7 @@ class Renderer:
                                         ray_begin, ray_end, _p(rgb), C.byref(st)))
         return rgb, dump
 
-    def render_device(self, cam, W, H, d_rgb, n_coarse=64, n_fine=128, precision="fp16", mode=SAMPLING_DET, seed=0,
+    def render_device(self, cam, W, H, d_rgb, n_coarse=64, n_fine=128, precision="mixed", mode=SAMPLING_DET, seed=0,
                       d_jitter=0, d_u=0, ray_begin=0, ray_end=None, stream=0):
         """render_image into a device buffer (int pointer), enqueued on `stream` (int cudaStream_t)."""
         ray_end = W * H if ray_end is None else ray_end
@@ -131,7 +131,7 @@ class Renderer:
                                         ray_begin, ray_end, d_rgb, stream))
 
     # ------------------------------------------------------------------ 8-bit output (save_ppm / pixels_to_rgba, lib.rs:567-592)
-    def render_rgb8(self, cam, W, H, n_coarse=64, n_fine=128, precision="fp16", mode=SAMPLING_DET, seed=0,
+    def render_rgb8(self, cam, W, H, n_coarse=64, n_fine=128, precision="mixed", mode=SAMPLING_DET, seed=0,
                     jitter=None, u=None, ray_begin=0, ray_end=None, channels=3):
         """render_image + the save_ppm quantiser on the device: uint8 [n, channels] (3 = PPM body, 4 = RGBA)."""
         ray_end = W * H if ray_end is None else ray_end
@@ -142,7 +142,7 @@ class Renderer:
                                       ray_begin, ray_end, channels, out.ctypes.data_as(C.POINTER(C.c_uint8))))
         return out
 
-    def render_many(self, cams, W, H, n_coarse=64, n_fine=128, precision="fp16", mode=SAMPLING_DET, seed=0, channels=3):
+    def render_many(self, cams, W, H, n_coarse=64, n_fine=128, precision="mixed", mode=SAMPLING_DET, seed=0, channels=3):
         """A batch of poses: uint8 [n_views, H * W, channels]; copies overlap the next view's render."""
         arr = (Camera * len(cams))(*cams)
         out = np.empty((len(cams), W * H, channels), np.uint8)
@@ -151,7 +151,7 @@ class Renderer:
                                       channels, out.ctypes.data_as(C.POINTER(C.c_uint8))))
         return out
 
-    def render_aux(self, cam, W, H, n_coarse=64, n_fine=128, precision="fp16", mode=SAMPLING_DET, seed=0,
+    def render_aux(self, cam, W, H, n_coarse=64, n_fine=128, precision="mixed", mode=SAMPLING_DET, seed=0,
                    jitter=None, u=None, ray_begin=0, ray_end=None):
         """render_image plus depth (sum w_i t_i) and accumulated opacity (sum w_i): (rgb [n,3], depth [n], acc [n])."""
         ray_end = W * H if ray_end is None else ray_end

@@ -67,7 +67,7 @@ def main():
             except Exception:
                 traceback.print_exc()
     frames = {}
-    for m in ("fp16x3", "fp16", "fp32"):
+    for m in ("fp16x3", "mixed", "fp16", "fp32"):
         try:
             out = np.empty((big * big, 3), np.float32)
             for it in range(2 if m != "fp32" else 1):
@@ -83,7 +83,7 @@ def main():
         except Exception:
             traceback.print_exc()
     if "fp32" in frames:
-        for m in ("fp16x3", "fp16"):
+        for m in ("fp16x3", "mixed", "fp16"):
             if m in frames:
                 d = np.abs(frames[m] - frames["fp32"])
                 mse = float(np.mean(d ** 2))

@@ -178,7 +178,7 @@ def test_render_tensor_core_psnr(renderer, cam, onets, ocam, prec, psnr_min):
     assert _psnr(got, want) >= psnr_min, (prec, _psnr(got, want), float(np.abs(got - want).max()) * 255)
 
 
-def test_render_fp16x3_meets_the_image_bound(renderer, cam, onets, ocam):
+def test_render_fp16x3_and_mixed_meet_the_image_bound(renderer, cam, onets, ocam):
     """North star: max per-pixel abs diff <= 2/255 and PSNR >= 45 dB against the reference render with identical,
     non-jittered sample positions - on the tensor cores.  Small frame against the CPU oracle; an 800-pixel-wide band
     through the object (rows 380..419 of the 800x800 frame) against the order-faithful f32 kernel, which the test
@@ -195,6 +195,12 @@ def test_render_fp16x3_meets_the_image_bound(renderer, cam, onets, ocam):
     assert f32.std() > 0.05  # the band crosses the object
     assert np.abs(x3 - f32).max() <= 2.0 / 255.0 and _psnr(x3, f32) >= 45.0
     assert _psnr(x3, f32) > 90.0
+    # "mixed": only the coarse network (which places the fine samples) runs fp16x3, the fine network single-pass fp16
+    mx = renderer.render_image(cam, W, H, 64, 128, precision="mixed", ray_begin=rb, ray_end=re_)
+    assert np.abs(mx - f32).max() <= 2.0 / 255.0 and _psnr(mx, f32) >= 80.0
+    # and that is where the 16-bit modes lose it: same fine network, single-pass coarse densities
+    fp16 = renderer.render_image(cam, W, H, 64, 128, precision="fp16", ray_begin=rb, ray_end=re_)
+    assert _psnr(fp16, f32) >= 50.0 and _psnr(mx, f32) > _psnr(fp16, f32) + 10.0
 
 
 def test_render_modes_and_ranges(renderer, cam, onets, ocam):
