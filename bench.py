@@ -303,6 +303,63 @@ def gpu_arm(args):
     r.close()
 
 
+def orbit_arm(args):
+    """BASELINE.json configs[4]: a synthetic orbit of `--orbit` poses at `--res`^2, views sharded across the ranks
+    (contiguous blocks, no data-path collective), each rank through nerf_render_many: 8-bit frames to pinned host
+    memory, the copy of view v overlapping the render of view v + 1.  Host wall clock around the whole sweep (the call
+    ends with every frame in host memory), max over ranks."""
+    import torch
+    import torch.distributed as dist
+    import nerf_rs_b200 as nb
+    from nerf_rs_b200 import shard
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: libnerf_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    r = nb.Renderer(nb.DATA_ROOT, device=local)
+    cams = nb.orbit_cameras(os.path.join(nb.DATA_ROOT, "tf_reference_samples.json"), args.orbit)
+    vb, ve = shard.ray_range(rank, world, args.orbit)  # the same contiguous split, over views
+    mine = cams[vb:ve]
+    R = args.res
+    r.render_many(mine[:1], R, R, NC, NF, precision=args.precision)  # warm-up: workspaces, pinned buffers, clocks
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = ClockSampler(local) if rank == 0 else None
+    t0 = time.perf_counter()
+    frames = r.render_many(mine, R, R, NC, NF, precision=args.precision)
+    torch.cuda.synchronize()
+    t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    clk = clocks.stop() if clocks else {}
+    checksum = int(frames.astype(np.uint64).sum()) if len(mine) else 0
+    if rank == 0:
+        dt = float(t.item())
+        n_rays = args.orbit * R * R
+        print(json.dumps({
+            "metric": "rays/s", "value": n_rays / dt, "unit": "rays/s", "n_gpus": world, "steps": 1, "warmup": 1,
+            "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "fp16" if args.precision == "mixed" else args.precision, "data": "synthetic",
+            "config": {"workload": f"orbit of {args.orbit} lego poses at {R}x{R}, 64 coarse + 128 fine samples/ray, "
+                                   "deterministic sampling, 8-bit frames returned to host memory",
+                       "precision": PRECISION_NOTE.get(args.precision, args.precision),
+                       "parallelism": f"views x{world} ({ve - vb} views on rank 0)"},
+            "samples_per_s": n_rays / dt * (NC + NC + NF), "views_per_s": args.orbit / dt,
+            "tflops": n_rays * (NC * FLOP_COARSE + (NC + NF) * FLOP_FINE) / dt / 1e12,
+            "d2h_bytes": n_rays * 3, "clocks": clk, "rank0_checksum": checksum}))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    r.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -311,9 +368,13 @@ def main():
     ap.add_argument("--precision", default="mixed", choices=["fp16", "bf16", "mixed", "fp16x3", "fp32"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--orbit", type=int, default=0, help="run the multi-pose sweep with this many views instead")
+    ap.add_argument("--res", type=int, default=1600, help="orbit sweep: frame width = height")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)
+    elif args.orbit > 0:
+        orbit_arm(args)
     else:
         gpu_arm(args)
 

@@ -124,6 +124,13 @@ int nerf_create(const char* weights_root, int device, nerf_ctx** out);
 /* Same from caller-held tensors (Network::new, network.rs:181-195). */
 int nerf_create_from_tensors(const nerf_tensor* coarse, int n_coarse, const nerf_tensor* fine, int n_fine, int device,
                              nerf_ctx** out);
+/* The pre-swizzled weight cache (one file per scene): the 2 x 24 f32 tensors of the weight directory plus the
+ * tensor-core chunk streams of every operand format, with a checksum.  nerf_build_weight_cache is host-only (no GPU):
+ * it runs load_network_from_dir (lib.rs:108-174) on <root>/coarse and <root>/fine and the tile builders, and writes
+ * the file; nerf_create_from_cache builds the same context nerf_create would, from one sequential read.  A missing,
+ * truncated or corrupted file is NERF_E_IO, a file of another version NERF_E_UNSUPPORTED. */
+int nerf_build_weight_cache(const char* weights_root, const char* cache_path);
+int nerf_create_from_cache(const char* cache_path, int device, nerf_ctx** out);
 void nerf_destroy(nerf_ctx*);
 
 /* Network::forward_batch (network.rs:197-237).  points: [3][B] feature-major (the reference's Matrix 3xB),

@@ -31,7 +31,11 @@ EXPORTS = ["nerf_last_error", "nerf_version", "nerf_create", "nerf_create_from_t
            "nerf_render_stages", "nerf_ray_dirs", "nerf_compute_weights", "nerf_sample_importance",
            "nerf_integrate_rays", "nerf_get_timing", "nerf_camera_from_json", "nerf_camera_from_values",
            "nerf_save_ppm", "nerf_quantize_rgb8", "nerf_render_rgb8", "nerf_render_rgb8_device", "nerf_render_many",
-           "nerf_quantize_rgb8_gpu", "nerf_render_aux", "nerf_render_aux_device"]
+           "nerf_quantize_rgb8_gpu", "nerf_render_aux", "nerf_render_aux_device", "nerf_build_weight_cache",
+           "nerf_create_from_cache"]
+
+
+E_ARG, E_IO, E_SHAPE, E_CUDA, E_UNSUPPORTED = -1, -2, -3, -4, -5  # nerf_status
 
 
 class NerfError(RuntimeError):
@@ -85,6 +89,8 @@ def lib():
     L.nerf_last_error.restype = C.c_char_p
     L.nerf_version.restype = C.c_char_p
     L.nerf_create.argtypes = [C.c_char_p, i32, C.POINTER(vp)]
+    L.nerf_build_weight_cache.argtypes = [C.c_char_p, C.c_char_p]
+    L.nerf_create_from_cache.argtypes = [C.c_char_p, i32, C.POINTER(vp)]
     L.nerf_create_from_tensors.argtypes = [C.POINTER(Tensor), i32, C.POINTER(Tensor), i32, i32, C.POINTER(vp)]
     L.nerf_destroy.argtypes = [vp]
     L.nerf_destroy.restype = None
@@ -141,6 +147,34 @@ def camera_from_values(near, far, origin, forward, up, hwf):
     _check(lib().nerf_camera_from_values(float(near), float(far), d3(*origin), d3(*forward), d3(*up), d3(*hwf),
                                          C.byref(cam)))
     return cam
+
+
+def build_weight_cache(weights_root, cache_path):
+    """Writes the pre-swizzled weight cache of a scene (host only, no GPU): the f32 tensors of
+    load_network_from_dir (src/lib.rs:108-174) plus the tensor-core chunk streams, one checksummed file."""
+    _check(lib().nerf_build_weight_cache(os.fsencode(weights_root), os.fsencode(cache_path)))
+
+
+def orbit_cameras(json_path, n_views):
+    """Synthetic poses of the throughput sweep: the JSON camera's radius and elevation,
+    azimuth theta_k = theta_0 + 2 pi k / n_views about +z (pose 0 is the JSON camera), forward = -pos / |pos| (the JSON
+    camera looks exactly at the origin), up = +z orthogonalised against forward, same near / far / hwf.  Each pose
+    goes through camera_from_samples (src/lib.rs:614-645) like the reference's own camera."""
+    import json
+    with open(json_path) as f:
+        d = json.load(f)
+    o = np.array(d["camera_origin"], np.float64)
+    radius, rho = float(np.linalg.norm(o)), float(np.hypot(o[0], o[1]))
+    theta0 = float(np.arctan2(o[1], o[0]))
+    cams = []
+    for k in range(n_views):
+        th = theta0 + 2.0 * np.pi * k / n_views
+        pos = np.array([rho * np.cos(th), rho * np.sin(th), o[2]])
+        fwd = -pos / radius
+        up = np.array([0.0, 0.0, 1.0]) - fwd[2] * fwd
+        up /= np.linalg.norm(up)
+        cams.append(camera_from_values(d["near"], d["far"], pos, fwd, up, d["hwf"]))
+    return cams
 
 
 def save_ppm(path, W, H, rgb):

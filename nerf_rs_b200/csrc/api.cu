@@ -10,6 +10,7 @@
 #include "common.cuh"
 #include "host_util.h"
 #include "mlp_tc.h"
+#include "weight_cache.h"
 
 namespace nerf {
 namespace {
@@ -98,7 +99,8 @@ struct DeviceGuard {
   }
 };
 
-int upload_network(const TensorMap& t, DeviceNet* net) {
+// `images`: the chunk streams of a weight cache file (one per operand format), or null to build them from `t`.
+int upload_network(const TensorMap& t, DeviceNet* net, const std::vector<uint8_t>* images = nullptr) {
   static const char* const names[12] = {"dense0", "dense1", "dense2", "dense3", "dense4", "dense5",
                                         "dense6", "dense7", "bottleneck", "viewdirs", "rgb", "alpha"};
   size_t total = 0;
@@ -131,14 +133,16 @@ int upload_network(const TensorMap& t, DeviceNet* net) {
   net->f32.w_rgb = dptr[20];   net->f32.b_rgb = dptr[21];
   net->f32.w_alpha = dptr[22]; net->f32.b_alpha = dptr[23];
   // Pre-swizzled 16-bit operand tiles for the tensor-core kernel, one set per operand format.
-  for (int fmt = 0; fmt < 2; ++fmt) {
-    int rc = build_tc_weights(t, fmt, net->f32, &net->tc[fmt]);
+  for (int fmt = 0; fmt < kNumTcFormats; ++fmt) {
+    TcWeights* w = fmt == 2 ? &net->tcx3 : &net->tc[fmt];
+    int rc = images ? upload_tc_weights(images[fmt].data(), images[fmt].size(), fmt, t, w) : build_tc_weights(t, fmt, w);
     if (rc != NERF_OK) return rc;
   }
-  return build_tc_x3_weights(t, &net->tcx3);
+  return NERF_OK;
 }
 
-int create_common(const TensorMap& coarse, const TensorMap& fine, int device, nerf_ctx** out) {
+int create_common(const TensorMap& coarse, const TensorMap& fine, int device, nerf_ctx** out,
+                  const CachedWeights* cache = nullptr) {
   int rc = validate_network(coarse, "coarse");
   if (rc != NERF_OK) return rc;
   rc = validate_network(fine, "fine");
@@ -184,8 +188,8 @@ int create_common(const TensorMap& coarse, const TensorMap& fine, int device, ne
     delete ctx;
     return NERF_E_CUDA;
   }
-  rc = upload_network(coarse, &ctx->nets[0]);
-  if (rc == NERF_OK) rc = upload_network(fine, &ctx->nets[1]);
+  rc = upload_network(coarse, &ctx->nets[0], cache ? cache->images[0] : nullptr);
+  if (rc == NERF_OK) rc = upload_network(fine, &ctx->nets[1], cache ? cache->images[1] : nullptr);
   if (rc != NERF_OK) {
     nerf_destroy(ctx);
     return rc;
@@ -375,6 +379,42 @@ int nerf_create(const char* weights_root, int device, nerf_ctx** out) {
   rc = load_tensor_dir(std::string(weights_root) + "/fine", &fine);  // lib.rs:652
   if (rc != NERF_OK) return rc;
   return create_common(coarse, fine, device, out);
+}
+
+int nerf_build_weight_cache(const char* weights_root, const char* cache_path) {
+  if (!weights_root || !cache_path) {
+    set_error("nerf_build_weight_cache: null argument");
+    return NERF_E_ARG;
+  }
+  TensorMap nets[2];
+  int rc = load_tensor_dir(std::string(weights_root) + "/coarse", &nets[0]);
+  if (rc == NERF_OK) rc = load_tensor_dir(std::string(weights_root) + "/fine", &nets[1]);
+  std::vector<uint8_t> blob;
+  if (rc == NERF_OK) rc = serialize_weight_cache(nets, &blob);
+  if (rc == NERF_OK) rc = write_file(cache_path, blob);
+  return rc;
+}
+
+int nerf_create_from_cache(const char* cache_path, int device, nerf_ctx** out) {
+  if (!cache_path || !out) {
+    set_error("nerf_create_from_cache: null argument");
+    return NERF_E_ARG;
+  }
+  std::vector<uint8_t> blob;
+  int rc = read_file(cache_path, &blob);
+  if (rc != NERF_OK) return rc;
+  CachedWeights cw;
+  rc = parse_weight_cache(blob.data(), blob.size(), &cw);
+  if (rc != NERF_OK) return rc;
+  for (int n = 0; n < 2; ++n) {  // a stream of the wrong length would make the kernel's bulk copies read past the end
+    for (int fmt = 0; fmt < kNumTcFormats; ++fmt) {
+      if (cw.images[n][fmt].size() != tc_image_bytes(fmt)) {
+        set_error("weight cache: chunk stream of unexpected size");
+        return NERF_E_SHAPE;
+      }
+    }
+  }
+  return create_common(cw.nets[0], cw.nets[1], device, out, &cw);
 }
 
 int nerf_create_from_tensors(const nerf_tensor* coarse, int n_coarse, const nerf_tensor* fine, int n_fine, int device,

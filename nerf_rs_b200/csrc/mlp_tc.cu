@@ -595,18 +595,35 @@ void append_chunk(std::vector<uint8_t>& img, const std::vector<float>& W, int ou
 
 }  // namespace
 
-int build_tc_weights(const TensorMap& t, int fmt, const NetF32&, TcWeights* out) {
-  std::vector<uint8_t> img;
-  img.reserve(1500 * 1024);
-  static const char* const names[10] = {"dense0", "dense1", "dense2", "dense3", "dense4",
-                                        "dense5", "dense6", "dense7", "bottleneck", "viewdirs"};
-  std::memset(&out->consts, 0, sizeof(out->consts));
+static const char* const kLayerNames[10] = {"dense0", "dense1", "dense2", "dense3", "dense4",
+                                            "dense5", "dense6", "dense7", "bottleneck", "viewdirs"};
+
+void fill_tc_consts(const TensorMap& t, TcConsts* c) {
+  std::memset(c, 0, sizeof(*c));
   for (int l = 0; l < kNumLayers; ++l) {
-    const std::vector<float>& W = t.at(std::string(names[l]) + "_kernel").data;
-    const std::vector<float>& b = t.at(std::string(names[l]) + "_bias").data;
+    const std::vector<float>& b = t.at(std::string(kLayerNames[l]) + "_bias").data;
+    for (int o = 0; o < layer_n(l); ++o) c->bias[l][o] = b[o];  // stays f32, added in the epilogue
+  }
+  const std::vector<float>& wa = t.at("alpha_kernel").data;
+  const std::vector<float>& wr = t.at("rgb_kernel").data;
+  for (int k = 0; k < 256; ++k) c->w_alpha[k] = wa[k];
+  for (int k = 0; k < 128 * 3; ++k) c->w_rgb[k] = wr[k];
+  for (int k = 0; k < 3; ++k) c->b_rgb[k] = t.at("rgb_bias").data[k];
+  c->b_alpha = t.at("alpha_bias").data[0];
+}
+
+void build_tc_image(const TensorMap& t, int fmt, std::vector<uint8_t>* out) {
+  if (fmt == 2) {
+    build_tc_x3_image(t, out);
+    return;
+  }
+  std::vector<uint8_t>& img = *out;
+  img.clear();
+  img.reserve(1500 * 1024);
+  for (int l = 0; l < kNumLayers; ++l) {
+    const std::vector<float>& W = t.at(std::string(kLayerNames[l]) + "_kernel").data;
     const int n = layer_n(l);
-    for (int o = 0; o < n; ++o) out->consts.bias[l][o] = b[o];
-    // K-block images in consumption order; the bias stays f32 (consts.bias) and is added in the epilogue
+    // K-block images in consumption order
     if (l == 0) {
       append_chunk(img, W, n, 0, kPosEnc, n, fmt);  // PE10 rows 0..62
     } else if (l == 5) {
@@ -619,21 +636,34 @@ int build_tc_weights(const TensorMap& t, int fmt, const NetF32&, TcWeights* out)
       for (int c = 0; c < 4; ++c) append_chunk(img, W, n, 64 * c, 64, n, fmt);
     }
   }
-  const std::vector<float>& wa = t.at("alpha_kernel").data;
-  const std::vector<float>& wr = t.at("rgb_kernel").data;
-  for (int k = 0; k < 256; ++k) out->consts.w_alpha[k] = wa[k];
-  for (int k = 0; k < 128 * 3; ++k) out->consts.w_rgb[k] = wr[k];
-  for (int k = 0; k < 3; ++k) out->consts.b_rgb[k] = t.at("rgb_bias").data[k];
-  out->consts.b_alpha = t.at("alpha_bias").data[0];
+}
+
+size_t tc_image_bytes(int fmt) {
+  size_t n = 0;
+  for (int l = 0; l < kNumLayers; ++l) {
+    const int kblocks = l == 0 ? 1 : ((l == 5 || l == 9) ? 5 : 4);  // 64-row K-blocks, encodings padded to 64
+    n += (size_t)kblocks * layer_n(l) * 128;
+  }
+  return fmt == 2 ? 2 * n : n;
+}
+
+int upload_tc_weights(const uint8_t* img, size_t bytes, int fmt, const TensorMap& t, TcWeights* out) {
+  fill_tc_consts(t, &out->consts);
   out->fmt = fmt;
-  out->bytes = img.size();
-  cudaError_t e = cudaMalloc(&out->d_chunks, img.size());
-  if (e == cudaSuccess) e = cudaMemcpy(out->d_chunks, img.data(), img.size(), cudaMemcpyHostToDevice);
+  out->bytes = bytes;
+  cudaError_t e = cudaMalloc(&out->d_chunks, bytes);
+  if (e == cudaSuccess) e = cudaMemcpy(out->d_chunks, img, bytes, cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
     set_error(std::string("upload tensor-core weight tiles: ") + cudaGetErrorString(e));
     return NERF_E_CUDA;
   }
   return NERF_OK;
+}
+
+int build_tc_weights(const TensorMap& t, int fmt, TcWeights* out) {
+  std::vector<uint8_t> img;
+  build_tc_image(t, fmt, &img);
+  return upload_tc_weights(img.data(), img.size(), fmt, t, out);
 }
 
 void free_tc_weights(TcWeights* w) {

@@ -1,6 +1,8 @@
 // mlp_tc.h — the fused tcgen05/TMEM MLP kernel (mlp_tc.cu): weight tiles, constants and launcher.
 #pragma once
 #include "common.cuh"
+#include <vector>
+
 #include "host_util.h"
 
 namespace nerf {
@@ -25,13 +27,19 @@ struct TcWeights {
   TcConsts consts;
 };
 
-int build_tc_weights(const TensorMap& t, int fmt, const NetF32& f32, TcWeights* out);
+// Operand formats: 0 = bf16, 1 = fp16 (mlp_tc.cu), 2 = fp16 hi / lo split, a hi and a lo chunk per K-block (mlp_tc_x3.cu).
+constexpr int kNumTcFormats = 3;
+// Host side (no GPU needed): the chunk stream of one network in one format, and the epilogue's f32 tables.
+void build_tc_image(const TensorMap& t, int fmt, std::vector<uint8_t>* out);
+void build_tc_x3_image(const TensorMap& t, std::vector<uint8_t>* out);
+void fill_tc_consts(const TensorMap& t, TcConsts* c);
+size_t tc_image_bytes(int fmt);  // length of that stream: the kernels' bulk copies read exactly this much
+// Device upload of a chunk stream (built just now, or read from a weight cache file).
+int upload_tc_weights(const uint8_t* img, size_t bytes, int fmt, const TensorMap& t, TcWeights* out);
+int build_tc_weights(const TensorMap& t, int fmt, TcWeights* out);
 void free_tc_weights(TcWeights* w);
 cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
                           cudaStream_t s);
-
-// fp16x3 mode (mlp_tc_x3.cu): every weight K-block as a hi and a lo fp16 chunk (fmt = 2), three MMAs per product.
-int build_tc_x3_weights(const TensorMap& t, TcWeights* out);
 cudaError_t launch_mlp_tc_x3(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
                              cudaStream_t s);
 

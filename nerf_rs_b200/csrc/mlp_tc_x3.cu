@@ -481,17 +481,15 @@ void append_split_chunks(std::vector<uint8_t>& img, const std::vector<float>& W,
 
 }  // namespace
 
-int build_tc_x3_weights(const TensorMap& t, TcWeights* out) {
-  std::vector<uint8_t> img;
+void build_tc_x3_image(const TensorMap& t, std::vector<uint8_t>* out) {
+  std::vector<uint8_t>& img = *out;
+  img.clear();
   img.reserve(2600 * 1024);
   static const char* const names[10] = {"dense0", "dense1", "dense2", "dense3", "dense4",
                                         "dense5", "dense6", "dense7", "bottleneck", "viewdirs"};
-  std::memset(&out->consts, 0, sizeof(out->consts));
   for (int l = 0; l < kNumLayers; ++l) {
     const std::vector<float>& W = t.at(std::string(names[l]) + "_kernel").data;
-    const std::vector<float>& b = t.at(std::string(names[l]) + "_bias").data;
     const int n = layer_n(l);
-    for (int o = 0; o < n; ++o) out->consts.bias[l][o] = b[o];
     if (l == 0) {
       append_split_chunks(img, W, n, 0, kPosEnc, n);  // PE10 rows 0..62
     } else if (l == 5) {
@@ -504,21 +502,6 @@ int build_tc_x3_weights(const TensorMap& t, TcWeights* out) {
       for (int c = 0; c < 4; ++c) append_split_chunks(img, W, n, 64 * c, 64, n);
     }
   }
-  const std::vector<float>& wa = t.at("alpha_kernel").data;
-  const std::vector<float>& wr = t.at("rgb_kernel").data;
-  for (int k = 0; k < 256; ++k) out->consts.w_alpha[k] = wa[k];
-  for (int k = 0; k < 128 * 3; ++k) out->consts.w_rgb[k] = wr[k];
-  for (int k = 0; k < 3; ++k) out->consts.b_rgb[k] = t.at("rgb_bias").data[k];
-  out->consts.b_alpha = t.at("alpha_bias").data[0];
-  out->fmt = 2;
-  out->bytes = img.size();
-  cudaError_t e = cudaMalloc(&out->d_chunks, img.size());
-  if (e == cudaSuccess) e = cudaMemcpy(out->d_chunks, img.data(), img.size(), cudaMemcpyHostToDevice);
-  if (e != cudaSuccess) {
-    set_error(std::string("upload fp16x3 weight tiles: ") + cudaGetErrorString(e));
-    return NERF_E_CUDA;
-  }
-  return NERF_OK;
 }
 
 cudaError_t launch_mlp_tc_x3(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,

@@ -48,11 +48,15 @@ class Network:
 
 
 class Renderer:
-    def __init__(self, weights_root=DATA_ROOT, device=0, tensors=None):
+    def __init__(self, weights_root=DATA_ROOT, device=0, tensors=None, cache=None):
         """weights_root holds coarse/ and fine/ (shapes.txt + *.bin).  `tensors` = (coarse_dict, fine_dict) of
-        name -> ndarray builds the context from memory instead (Network::new, network.rs:181-195)."""
+        name -> ndarray builds the context from memory instead (Network::new, network.rs:181-195); `cache` = path of a
+        file written by build_weight_cache."""
         h = C.c_void_p()
-        if tensors is not None:
+        if cache is not None:
+            import os
+            _check(lib().nerf_create_from_cache(os.fsencode(cache), device, C.byref(h)))
+        elif tensors is not None:
             keep = []
 
             def pack(d):

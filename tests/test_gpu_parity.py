@@ -341,3 +341,24 @@ def test_render_aux_depth_and_opacity(renderer, cam):
     assert np.abs(rgb - (colour + (1.0 - acc[:, None]))).max() < 1e-5
     part = renderer.render_aux(cam, W, H, nc, nf, precision="fp32", ray_begin=50, ray_end=200)
     assert (part[1] == depth[50:200]).all() and (part[2] == acc[50:200]).all()
+
+
+def test_context_from_weight_cache_is_bit_identical(renderer, cam, tmp_path):
+    """a context built from the pre-swizzled cache file renders and evaluates exactly what the
+    context built from the weight directory does, in every precision mode."""
+    path = str(tmp_path / "lego.nrfw")
+    nb.build_weight_cache(nb.DATA_ROOT, path)
+    r2 = nb.Renderer(cache=path, device=0)
+    try:
+        rng = np.random.default_rng(3)
+        pts = rng.uniform(-1.5, 1.5, (3, 777)).astype(np.float32)
+        dirs = rng.normal(size=(777, 3)).astype(np.float32)
+        dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+        for prec in ("fp32", "bf16", "fp16", "fp16x3"):
+            for a, b in ((renderer.coarse, r2.coarse), (renderer.fine, r2.fine)):
+                ra, sa = a.forward_batch(pts, dirs, precision=prec)
+                rb, sb = b.forward_batch(pts, dirs, precision=prec)
+                assert (ra == rb).all() and (sa == sb).all(), prec
+        assert (renderer.render_image(cam, 16, 16, 64, 128) == r2.render_image(cam, 16, 16, 64, 128)).all()
+    finally:
+        r2.close()

@@ -223,3 +223,64 @@ def test_integrate_aux_closed_form():
     assert tuple(O.integrate_aux(np.zeros(0, np.float32), np.zeros(0, np.float32), far)) == (0.0, 0.0)
     d0, a0 = O.integrate_aux(np.zeros(n, np.float32), t, far)  # empty space
     assert d0 == 0.0 and a0 == 0.0
+
+
+def test_orbit_cameras_pose0_is_the_json_camera_and_views_shard():
+    """The throughput sweep's synthetic poses (BASELINE.json configs[4]): pose 0 is the reference camera, every pose
+    keeps its radius / elevation, looks at the origin with an orthonormal basis, and the contiguous view split used by
+    `bench.py --orbit` covers all views exactly once."""
+    import nerf_rs_b200 as nb
+    from nerf_rs_b200 import shard
+    from tests.conftest import CAM_JSON
+    c0 = nb.camera_from_json(CAM_JSON)
+    cams = nb.orbit_cameras(CAM_JSON, 200)
+    assert len(cams) == 200
+    for f in ("origin", "forward", "up"):
+        assert np.abs(np.array(getattr(c0, f)[:]) - np.array(getattr(cams[0], f)[:])).max() < 2e-7
+    assert cams[0].alpha_w == c0.alpha_w and cams[0].alpha_h == c0.alpha_h
+    r0, z0 = np.linalg.norm(c0.origin[:]), c0.origin[2]
+    for c in cams[::17]:
+        o, f, u = (np.array(x[:], np.float64) for x in (c.origin, c.forward, c.up))
+        assert abs(np.linalg.norm(o) - r0) < 1e-5 and abs(o[2] - z0) < 1e-6
+        assert np.abs(f + o / np.linalg.norm(o)).max() < 1e-6 and abs(f @ u) < 1e-6 and abs(np.linalg.norm(u) - 1) < 1e-6
+        assert (c.near, c.far) == (c0.near, c0.far)
+    a = np.arctan2(cams[50].origin[1], cams[50].origin[0]) - np.arctan2(c0.origin[1], c0.origin[0])
+    assert abs((a % (2 * np.pi)) - np.pi / 2) < 1e-5  # a quarter turn after 50 of 200 views
+    for world in (1, 2, 3, 8):
+        got = [v for r in range(world) for v in range(*shard.ray_range(r, world, 200))]
+        assert got == list(range(200))
+
+
+def test_weight_cache_file_is_deterministic_and_checked(tmp_path):
+    """nerf_build_weight_cache (host only): same bytes every time, holds the 2 x 24 f32 tensors bit for bit, and a
+    loader refuses a truncated / corrupted / foreign file before touching the GPU (checksum first, then device)."""
+    import struct
+    import nerf_rs_b200 as nb
+    a, b = str(tmp_path / "a.nrfw"), str(tmp_path / "b.nrfw")
+    nb.build_weight_cache(DATA, a)
+    nb.build_weight_cache(DATA, b)
+    raw = open(a, "rb").read()
+    assert raw == open(b, "rb").read()
+    assert raw[:8] == b"NRFB200W" and struct.unpack_from("<II", raw, 8) == (1, 2)
+    # two nets x (f32 tensors + bf16 + fp16 + split-fp16 streams): 2 x (2 383 376 + 1 196 032 x 4) B + names / dims
+    assert 2 * (2383376 + 4 * 1196032) < len(raw) < 2 * (2383376 + 4 * 1196032) + 4096
+    w = np.fromfile(os.path.join(DATA, "fine", "dense5_kernel.bin"), np.float32)
+    assert raw.count(w.tobytes()) == 1  # stored verbatim
+    with pytest.raises(nb.NerfError) as e:
+        nb.build_weight_cache(str(tmp_path / "nowhere"), a)
+    assert e.value.code == nb.E_IO
+    import ctypes as C
+    h = C.c_void_p()
+    L = nb.lib()
+    bad = bytearray(raw)
+    bad[len(bad) // 2] ^= 0x40
+    for name, blob in (("flip", bytes(bad)), ("trunc", raw[:-100]), ("magic", b"XXXXXXXX" + raw[8:]), ("empty", b"")):
+        path = str(tmp_path / name)
+        open(path, "wb").write(blob)
+        assert L.nerf_create_from_cache(os.fsencode(path), 0, C.byref(h)) == nb.E_IO, name
+        assert b"weight cache" in L.nerf_last_error()
+    assert L.nerf_create_from_cache(os.fsencode(str(tmp_path / "missing")), 0, C.byref(h)) == nb.E_IO
+    # an intact file gets as far as the device: no GPU here, no CPU fallback
+    from tests.conftest import _have_gpu
+    if not _have_gpu():
+        assert L.nerf_create_from_cache(os.fsencode(a), 0, C.byref(h)) == nb.E_CUDA
