@@ -162,17 +162,28 @@ def gpu_arm(args):
     n_rays = W * H
     rb, re_ = shard.ray_range(rank, world, n_rays)
     n_local = re_ - rb
-    frame = torch.empty((n_rays, 3), dtype=torch.float32, device=dev)  # rank 0 assembles the frame here
-    mine = frame[rb:re_] if world == 1 else torch.empty((n_local, 3), dtype=torch.float32, device=dev)
+    use_peer = world > 1 and args.gather == "peer"
+    sf = None
+    if use_peer:
+        # the frame lives in rank 0's HBM; every rank maps it (CUDA IPC) and its compositing kernel stores there
+        sf = shard.SharedFrame(r, n_rays, rank, world, dist)
+        frame = sf.tensor() if rank == 0 else None
+        mine = None
+        mine_ptr = sf.row_ptr(rb)
+    else:
+        frame = torch.empty((n_rays, 3), dtype=torch.float32, device=dev)  # rank 0 assembles the frame here
+        mine = frame[rb:re_] if world == 1 else torch.empty((n_local, 3), dtype=torch.float32, device=dev)
+        mine_ptr = mine.data_ptr()
     pinned = torch.empty((n_rays, 3), dtype=torch.float32).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream()
 
     def gather():
-        shard.gather_frame(mine, frame if rank == 0 else None, rank, world, dist)
+        if not use_peer:  # peer mode: the pixels are already in rank 0's buffer when the kernel retires
+            shard.gather_frame(mine, frame if rank == 0 else None, rank, world, dist)
 
     def step_device(prec=None):
-        r.render_device(cam, W, H, mine.data_ptr(), NC, NF, precision=prec or args.precision, ray_begin=rb, ray_end=re_,
+        r.render_device(cam, W, H, mine_ptr, NC, NF, precision=prec or args.precision, ray_begin=rb, ray_end=re_,
                         stream=stream.cuda_stream)
         gather()
 
@@ -181,6 +192,8 @@ def gpu_arm(args):
             r.render_image(cam, W, H, NC, NF, precision=args.precision, out=pinned.numpy())  # host API, syncs
         else:
             step_device()
+            if use_peer:
+                sf.complete(stream)  # every rank's stores have landed in rank 0's HBM
             if rank == 0:
                 pinned.copy_(frame, non_blocking=True)
             stream.synchronize()
@@ -258,7 +271,10 @@ def gpu_arm(args):
             "vs_baseline": None, "dtype": "fp16" if args.precision == "mixed" else args.precision, "data": "synthetic",
             "config": {"workload": WORKLOAD, "precision": PRECISION_NOTE.get(args.precision, args.precision), "parallelism": f"ray-range x{world}",
                        "l2": "flushed (256 MiB memset, untimed) before every step; per-frame intermediates ~3 GB >> 126 MB L2",
-                       "gather": "NCCL point-to-point group: every rank sends its rgb range to rank 0, inside the timed region" if world > 1 else "none"},
+                       "gather": ("none" if world == 1 else
+                                  "peer stores: every rank's compositing kernel writes its rows into rank 0's frame buffer over "
+                                  "NVLink (CUDA IPC mapping), inside the timed region; no collective on the data path" if use_peer else
+                                  "NCCL point-to-point group: every rank sends its rgb range to rank 0, inside the timed region")},
             "samples_per_s": value * (NC + NC + NF),
             "tflops_frame": n_rays * (NC * FLOP_COARSE + (NC + NF) * FLOP_FINE) / (ms * 1e-3) / 1e12 ,
             "stage_ms_rank0": {"mlp_coarse": mc, "mlp_fine": mf, "sampling": sm_ms, "composite": cp_ms},
@@ -297,6 +313,14 @@ def gpu_arm(args):
                                     "sample": f"{n} rays of the same frame (pixel indices {begin}..{begin + n}), "
                                               f"{dt:.1f} s, oracle reordered bit-identical GEMM loop"}
         print(json.dumps(line))
+    if sf is not None:
+        frame = None
+        dist.barrier()
+        if rank != 0:
+            sf.close()  # unmap before the owner frees
+        dist.barrier()
+        if rank == 0:
+            sf.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -368,6 +392,8 @@ def main():
     ap.add_argument("--precision", default="mixed", choices=["fp16", "bf16", "mixed", "fp16x3", "fp32"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: peer = compositing kernels store into rank 0's frame over NVLink; nccl = send/recv gather")
     ap.add_argument("--orbit", type=int, default=0, help="run the multi-pose sweep with this many views instead")
     ap.add_argument("--res", type=int, default=1600, help="orbit sweep: frame width = height")
     args = ap.parse_args()

@@ -176,6 +176,18 @@ int nerf_render_aux_device(nerf_ctx*, const nerf_camera*, int W, int H, int n_co
                            const nerf_sampling*, int64_t ray_begin, int64_t ray_end, float* d_rgb, float* d_depth,
                            float* d_acc, void* stream);
 
+/* Multi-GPU frame assembly without a collective (one process per GPU; the reference's counterpart is rayon's collect
+ * + scatter into the image, lib.rs:533-557).  Rank 0 creates the frame buffer in its HBM and publishes the 64-byte
+ * CUDA IPC handle (over any side channel); every other rank opens it and passes `ptr + 12 * ray_begin` as d_rgb to
+ * nerf_render_device / nerf_render_aux_device for its own [ray_begin, ray_end): the compositing kernel then stores
+ * its pixels straight into rank 0's buffer over NVLink - the gather is fused into the producing kernel.  The frame
+ * is complete on rank 0 once every rank's stream has been synchronised (a host barrier).  `owner` = 1 frees the
+ * allocation, 0 unmaps it. */
+#define NERF_IPC_HANDLE_BYTES 64
+int nerf_shared_frame_create(nerf_ctx*, uint64_t bytes, void** d_ptr, unsigned char handle[NERF_IPC_HANDLE_BYTES]);
+int nerf_shared_frame_open(nerf_ctx*, const unsigned char handle[NERF_IPC_HANDLE_BYTES], void** d_ptr);
+int nerf_shared_frame_close(nerf_ctx*, void* d_ptr, int owner);
+
 /* Stage entry points (host buffers), one per reference function, used by the stage-wise parity tests. */
 int nerf_ray_dirs(nerf_ctx*, const nerf_camera*, int W, int H, int64_t ray_begin, int64_t ray_end,
                   float* dirs /*[n][3]*/);                                   /* lib.rs:214-230 + :371 */

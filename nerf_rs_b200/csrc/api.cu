@@ -910,6 +910,55 @@ int nerf_integrate_rays(nerf_ctx* c, const float* rgb, const float* sigma, const
   return NERF_OK;
 }
 
+// ---------------------------------------------------------------------------------------- shared frame (multi-GPU)
+int nerf_shared_frame_create(nerf_ctx* c, uint64_t bytes, void** d_ptr, unsigned char handle[NERF_IPC_HANDLE_BYTES]) {
+  if (!c || !d_ptr || !handle || bytes == 0) {
+    set_error("nerf_shared_frame_create: bad argument");
+    return NERF_E_ARG;
+  }
+  static_assert(sizeof(cudaIpcMemHandle_t) == NERF_IPC_HANDLE_BYTES, "CUDA IPC handle size");
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  void* p = nullptr;
+  NERF_CUDA(cudaMalloc(&p, bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    set_error(std::string("cudaIpcGetMemHandle: ") + cudaGetErrorString(e));
+    return NERF_E_CUDA;
+  }
+  std::memcpy(handle, &h, sizeof(h));
+  *d_ptr = p;
+  return NERF_OK;
+}
+
+int nerf_shared_frame_open(nerf_ctx* c, const unsigned char handle[NERF_IPC_HANDLE_BYTES], void** d_ptr) {
+  if (!c || !d_ptr || !handle) {
+    set_error("nerf_shared_frame_open: bad argument");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle, sizeof(h));
+  void* p = nullptr;
+  // maps the owner's allocation into this process and enables peer access between the two devices (NVLink)
+  NERF_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  *d_ptr = p;
+  return NERF_OK;
+}
+
+int nerf_shared_frame_close(nerf_ctx* c, void* d_ptr, int owner) {
+  if (!c || !d_ptr) return NERF_OK;
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  NERF_CUDA(cudaDeviceSynchronize());
+  if (owner) NERF_CUDA(cudaFree(d_ptr));
+  else NERF_CUDA(cudaIpcCloseMemHandle(d_ptr));
+  return NERF_OK;
+}
+
 int nerf_get_timing(nerf_ctx* c, nerf_timing* out) {
   if (!c || !out) {
     set_error("nerf_get_timing: null argument");

@@ -38,3 +38,57 @@ def gather_frame(local, frame, rank, world, dist=None, group=None):
         for w in dist.batch_isend_irecv([dist.P2POp(dist.isend, local, 0, group)]):
             w.wait()
     return None
+
+
+class SharedFrame:
+    """The frame buffer of a multi-GPU render, in rank 0's HBM, mapped into every rank through CUDA IPC
+    (nerf_shared_frame_*): each rank renders its ray range with `d_rgb = frame.row_ptr(ray_begin)`, so the compositing
+    kernel's stores go straight to rank 0 over NVLink and no collective moves pixels.  `complete()` is the only
+    synchronisation: every rank drains its stream, then a barrier."""
+
+    def __init__(self, renderer, n_rays, rank, world, dist=None, group=None, channels=3, itemsize=4):
+        import ctypes as C
+        from . import _check, lib
+        self.renderer, self.rank, self.world, self.dist, self.group = renderer, rank, world, dist, group
+        self.n_rays, self.row_bytes = n_rays, channels * itemsize
+        self.channels = channels
+        ptr = C.c_void_p()
+        if rank == 0:
+            buf = C.create_string_buffer(64)
+            _check(lib().nerf_shared_frame_create(renderer._h, n_rays * self.row_bytes, C.byref(ptr), buf))
+            handle = [buf.raw]
+        else:
+            handle = [None]
+        if world > 1:
+            dist.broadcast_object_list(handle, src=0, group=group)  # 64 bytes over the control plane
+        if rank != 0:
+            _check(lib().nerf_shared_frame_open(renderer._h, handle[0], C.byref(ptr)))
+        self.handle = handle[0]
+        self.ptr = ptr.value
+
+    def row_ptr(self, ray):
+        return self.ptr + ray * self.row_bytes
+
+    def complete(self, stream=None):
+        """Returns once every rank's pixels are in rank 0's buffer."""
+        if stream is not None:
+            stream.synchronize()
+        if self.world > 1:
+            self.dist.barrier(group=self.group)
+
+    def tensor(self):
+        """Rank 0: the frame as a torch tensor aliasing the buffer (float32 [n_rays, channels])."""
+        import torch
+
+        class _Raw:
+            pass
+        raw = _Raw()
+        raw.__cuda_array_interface__ = {"shape": (self.n_rays, self.channels), "typestr": "<f4",
+                                        "data": (self.ptr, False), "version": 2}
+        return torch.as_tensor(raw, device=torch.device("cuda", self.renderer.device))
+
+    def close(self):
+        from . import _check, lib
+        if self.ptr:
+            _check(lib().nerf_shared_frame_close(self.renderer._h, self.ptr, 1 if self.rank == 0 else 0))
+            self.ptr = 0

@@ -362,3 +362,54 @@ def test_context_from_weight_cache_is_bit_identical(renderer, cam, tmp_path):
         assert (renderer.render_image(cam, 16, 16, 64, 128) == r2.render_image(cam, 16, 16, 64, 128)).all()
     finally:
         r2.close()
+
+
+_PEER_CHILD = r"""
+import sys, ctypes as C
+sys.path.insert(0, sys.argv[1])
+import nerf_rs_b200 as nb
+handle, W, H, rb, re_ = bytes.fromhex(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5]), int(sys.argv[6])
+r = nb.Renderer(nb.DATA_ROOT, device=0)
+cam = nb.camera_from_json(nb.DATA_ROOT + "/tf_reference_samples.json")
+p = C.c_void_p()
+assert nb.lib().nerf_shared_frame_open(r._h, handle, C.byref(p)) == 0, nb.lib().nerf_last_error()
+r.render_device(cam, W, H, p.value + 12 * rb, 64, 128, precision="mixed", ray_begin=rb, ray_end=re_)
+import torch
+torch.cuda.synchronize()
+assert nb.lib().nerf_shared_frame_close(r._h, p, 0) == 0
+r.close()
+print("child ok")
+"""
+
+
+def test_shared_frame_second_process_stores_into_the_owner_buffer(renderer, cam):
+    """the frame buffer lives with rank 0, every other rank (one process per GPU) maps it through CUDA
+    IPC and its compositing kernel stores its ray range there.  Here the second process shares the one GPU of the test
+    box; with one process per GPU the same mapping goes over NVLink.  The assembled frame is bit-identical to the
+    single-process frame."""
+    import ctypes as C
+    import subprocess
+    import sys
+    import torch
+    from nerf_rs_b200 import shard
+    from tests.conftest import ROOT
+    W, H = 48, 40
+    n = W * H
+    sf = shard.SharedFrame(renderer, n, 0, 1)
+    try:
+        assert len(sf.handle) == 64 and sf.ptr
+        frame = sf.tensor()
+        frame.zero_()
+        torch.cuda.synchronize()
+        half = shard.ray_range(1, 2, n)[0]
+        child = subprocess.run([sys.executable, "-c", _PEER_CHILD, ROOT, sf.handle.hex(), str(W), str(H), str(half), str(n)],
+                               capture_output=True, text=True, timeout=300)
+        assert child.returncode == 0 and "child ok" in child.stdout, child.stderr[-2000:]
+        renderer.render_device(cam, W, H, sf.row_ptr(0), 64, 128, precision="mixed", ray_begin=0, ray_end=half)
+        sf.complete(torch.cuda.current_stream())
+        torch.cuda.synchronize()
+        got = frame.cpu().numpy()
+        want = renderer.render_image(cam, W, H, 64, 128, precision="mixed")
+        assert (got == want).all()
+    finally:
+        sf.close()
