@@ -413,3 +413,59 @@ def test_shared_frame_second_process_stores_into_the_owner_buffer(renderer, cam)
         assert (got == want).all()
     finally:
         sf.close()
+
+
+def _random_scene(root, seed):
+    """Two random networks in the reference's weight-directory format (lego_rust/README.md:23-36): shapes.txt +
+    <name>.bin, little-endian f32.  He-style scales keep activations O(1); biases are non-zero."""
+    import os
+    rng = np.random.default_rng(seed)
+    shapes = [l.split() for l in open(os.path.join(nb.DATA_ROOT, "coarse", "shapes.txt")) if l.strip()]
+    nets = []
+    for net in ("coarse", "fine"):
+        os.makedirs(os.path.join(root, net))
+        d = {}
+        for name, *dims in shapes:
+            dims = [int(x) for x in dims]
+            if name.endswith("_kernel"):
+                a = rng.normal(0.0, np.sqrt(2.0 / dims[0]), dims)
+            else:
+                a = rng.normal(0.0, 0.1, dims)
+            if name == "alpha_bias":
+                a = a + 1.0  # keep a good share of the densities above the ReLU knee
+            d[name] = a.astype(np.float32)
+            d[name].tofile(os.path.join(root, net, name + ".bin"))
+        with open(os.path.join(root, net, "shapes.txt"), "w") as f:
+            f.writelines(" ".join(s) + "\n" for s in shapes)
+        nets.append(d)
+    return nets
+
+
+def test_other_weights_from_tensors_directory_and_cache(cam, ocam, tmp_path):
+    """Network::new (network.rs:181-195) through nerf_create_from_tensors, on weights that are not the lego ones: the
+    context from caller-held tensors, the one from the same tensors written as a weight directory and the one from
+    that directory's cache file are the same bit for bit, and match the oracle loading the directory."""
+    root = str(tmp_path / "scene")
+    coarse, fine = _random_scene(root, seed=7)
+    onet_c, onet_f = O.Network(root + "/coarse"), O.Network(root + "/fine")
+    assert (onet_f.tensor("dense5_kernel") == fine["dense5_kernel"].ravel()).all()
+    nb.build_weight_cache(root, root + "/scene.nrfw")
+    rs = [nb.Renderer(tensors=(coarse, fine), device=0), nb.Renderer(root, device=0),
+          nb.Renderer(cache=root + "/scene.nrfw", device=0)]
+    try:
+        pts, dirs = _random_samples(ocam, 1500, seed=21)
+        for which, onet in ((0, onet_c), (1, onet_f)):
+            rgb_ref, sig_ref = onet.forward_batch(pts, dirs)
+            assert sig_ref.max() > 0.5 and (sig_ref > 0).mean() > 0.2  # the test has something to compare
+            for prec in ("fp32", "fp16x3", "fp16", "bf16"):
+                outs = [(r.coarse, r.fine)[which].forward_batch(pts, dirs, precision=prec) for r in rs]
+                for rgb, sig in outs[1:]:
+                    assert (rgb == outs[0][0]).all() and (sig == outs[0][1]).all(), prec
+                _check(prec, outs[0][0], outs[0][1], rgb_ref, sig_ref)
+        want = O.render(onet_c, onet_f, ocam, 16, 16, 64, 128)
+        for prec, tol in (("fp32", 2e-3), ("fp16x3", 2e-3)):
+            got = rs[0].render_image(cam, 16, 16, 64, 128, precision=prec)
+            assert np.abs(got - want).max() < tol, (prec, float(np.abs(got - want).max()))
+    finally:
+        for r in rs:
+            r.close()
