@@ -166,7 +166,22 @@ def gpu_arm(args):
     sf = None
     if use_peer:
         # the frame lives in rank 0's HBM; every rank maps it (CUDA IPC) and its compositing kernel stores there
-        sf = shard.SharedFrame(r, n_rays, rank, world, dist)
+        try:
+            sf = shard.SharedFrame(r, n_rays, rank, world, dist)
+            ok = 1
+        except Exception as e:  # no peer mapping on this box: all ranks fall back to the NCCL gather together
+            print(f"rank {rank}: shared frame unavailable ({e}); using the NCCL gather", file=sys.stderr)
+            sf, ok = None, 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            if sf is not None and rank != 0:
+                sf.close()
+            dist.barrier()
+            if sf is not None and rank == 0:
+                sf.close()
+            sf, use_peer = None, False
+    if use_peer:
         frame = sf.tensor() if rank == 0 else None
         mine = None
         mine_ptr = sf.row_ptr(rb)

@@ -53,14 +53,18 @@ class SharedFrame:
         self.n_rays, self.row_bytes = n_rays, channels * itemsize
         self.channels = channels
         ptr = C.c_void_p()
+        handle, err = [None], None
         if rank == 0:
             buf = C.create_string_buffer(64)
-            _check(lib().nerf_shared_frame_create(renderer._h, n_rays * self.row_bytes, C.byref(ptr), buf))
-            handle = [buf.raw]
-        else:
-            handle = [None]
+            rc = lib().nerf_shared_frame_create(renderer._h, n_rays * self.row_bytes, C.byref(ptr), buf)
+            if rc == 0:
+                handle = [buf.raw]
+            else:
+                err = lib().nerf_last_error().decode()
         if world > 1:
             dist.broadcast_object_list(handle, src=0, group=group)  # 64 bytes over the control plane
+        if handle[0] is None:  # every rank learns of rank 0's failure through the broadcast: nobody is left waiting
+            raise RuntimeError("shared frame: rank 0 could not create it" + (f" ({err})" if err else ""))
         if rank != 0:
             _check(lib().nerf_shared_frame_open(renderer._h, handle[0], C.byref(ptr)))
         self.handle = handle[0]
