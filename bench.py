@@ -66,11 +66,14 @@ def cpu_sample(threads=0, budget_s=15.0):
     return O, (oc, of, cam), cores, begin, n
 
 
-def run_cpu_step(ctx, cores, begin, n):
+def run_cpu_step(ctx, cores, begin, n, keep=None):
     O, (oc, of, cam) = ctx
     t0 = time.perf_counter()
-    O.render(oc, of, cam, W, H, NC, NF, ray_begin=begin, ray_end=begin + n, threads=cores)
-    return time.perf_counter() - t0
+    img = O.render(oc, of, cam, W, H, NC, NF, ray_begin=begin, ray_end=begin + n, threads=cores)
+    dt = time.perf_counter() - t0
+    if keep is not None:
+        keep.append(img)
+    return dt
 
 
 def reference_arm(args):
@@ -323,7 +326,15 @@ def gpu_arm(args):
                 "frac_of_burst": c_ach / burst, "executed_frac_of_burst": 3 * c_ach / burst}
         if world == 1 and not args.no_cpu:
             O, ctx, cores, begin, n = cpu_sample()
-            dt = run_cpu_step((O, ctx), cores, begin, n)
+            band = []
+            dt = run_cpu_step((O, ctx), cores, begin, n, keep=band)
+            # BASELINE.json's metric ends "PSNR vs ref": the rows the CPU arm just rendered against the same rows of the
+            # frame the e2e leg left in host memory (identical deterministic sample positions on both sides)
+            d = np.abs(pinned.numpy()[begin:begin + n] - band[0])
+            line["parity"] = {"vs": "CPU oracle (the reference's algorithm restated), same rays, same sample positions",
+                              "rays": n, "max_abs_diff_x255": float(d.max() * 255.0),
+                              "pixels_over_2_255": int((d.max(axis=1) > 2.0 / 255.0).sum()),
+                              "psnr_db": float(10.0 * np.log10(1.0 / max(float(np.mean(d.astype(np.float64) ** 2)), 1e-20)))}
             line["cpu_baseline"] = {"value": n / dt, "unit": "rays/s", "cores": cores, "kind": "port",
                                     "sample": f"{n} rays of the same frame (pixel indices {begin}..{begin + n}), "
                                               f"{dt:.1f} s, oracle reordered bit-identical GEMM loop"}
