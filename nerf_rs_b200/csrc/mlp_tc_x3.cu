@@ -48,6 +48,8 @@ constexpr uint32_t kOffBar = kOffStage + kStages * kStageBytes;
 constexpr uint32_t kBarFull = 0, kBarPFull = 32, kBarEmpty = 64, kBarAcc = 96, kBarAct = 104, kTmemSlotOff = 128;
 constexpr uint32_t kSmemBytes = kOffBar + 256;
 static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
+static_assert(kOffActLo - kOffActHi == kActBytes && kOffAuxLo - kOffAuxHi == kAuxBytes,
+              "the epilogue and the MMA issuer address a lo image as its hi image + one tile");
 constexpr int kEpiRegs = 112, kCtlRegs = 32;
 constexpr int kNumLayers = 10;  // dense0..7, bottleneck, viewdirs
 
