@@ -258,6 +258,28 @@ def test_cli_writes_the_same_ppm(renderer, cam, tmp_path):
     data = (tmp_path / "output.ppm").read_bytes()
     assert data.startswith(b"P6\n256 256\n255\n") and len(data) == 15 + 256 * 256 * 3
     assert "Rendering with 64 coarse samples and 128 fine samples per ray" in r.stdout
+    # --cache: first run writes the pre-swizzled weight cache, second run starts from it; same bytes as from the directory
+    cache = tmp_path / "lego.nrfw"
+    outs = []
+    for k in range(2):
+        o = tmp_path / f"cache{k}.ppm"
+        r = subprocess.run([cli, "--weights", nb.DATA_ROOT, "--cache", str(cache), "--width", "32", "--height", "24", "--det",
+                            "--out", str(o)], capture_output=True, text=True)
+        assert r.returncode == 0 and cache.exists(), r.stderr
+        outs.append(o.read_bytes())
+    mixed = renderer.render_image(cam, 32, 24, 64, 128)  # the CLI's default precision is the library's: mixed
+    assert outs[0] == outs[1] == b"P6\n32 24\n255\n" + nb.quantize_rgb8(mixed).tobytes()
+    # --gpus N: one context and one host thread per device, contiguous pixel-index ranges (rayon's role, lib.rs:533-550)
+    import torch
+    n = min(torch.cuda.device_count(), 4)
+    o = tmp_path / "multi.ppm"
+    r = subprocess.run([cli, "--weights", nb.DATA_ROOT, "--gpus", str(n), "--width", "32", "--height", "24", "--det", "--out",
+                        str(o)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert o.read_bytes() == outs[0] and r.stdout.count("device time") == n
+    r = subprocess.run([cli, "--weights", nb.DATA_ROOT, "--gpus", str(torch.cuda.device_count() + 1)], capture_output=True,
+                       text=True, cwd=tmp_path)
+    assert r.returncode == 1 and "device ordinal out of range" in r.stderr
 
 
 # ---------------------------------------------------------------- 8-bit output on the device
