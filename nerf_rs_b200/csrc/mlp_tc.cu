@@ -10,20 +10,20 @@
 //   - B (weights) is split by N between the two CTAs: each CTA streams only its [N/2 x 64] half of every chunk
 //     (16 KiB) from L2 with 1-D bulk TMA copies into a four-deep ring.  Both slots consume a chunk before it is
 //     released, so L2 -> SMEM traffic is one weight pass per four tiles.
-//   - Bias never goes through the tensor core: after an epilogue thread has read a block of accumulator columns it
-//     writes the NEXT layer's bias (exact f32) back into them with tcgen05.st, and every MMA accumulates.
+//   - Bias never goes through the tensor core: the epilogue adds it in f32 to the accumulator values it has just
+//     read, from the kernel's constant bank (TcConsts is a __grid_constant__ parameter), before ReLU and rounding.
 //   - The issue order is static: slot X's layer l, then slot Y's layer l, then X's layer l + 1, ...  The single
 //     MMA thread blocks on one barrier at a time and runs ahead of the tensor pipe, so while slot X's epilogue
 //     drains layer l the pipe is busy with Y's layer l (already queued) and vice versa.  A 256-wide layer is four
-//     chunks = the whole ring; the only five-chunk layer (dense5) is issued X0-3, Y0-2, X4, Y3-4.
+//     chunks = the whole ring; the only five-chunk layer (dense5) is issued X0-3, Y0, X4, Y1-4.
 //   - concat_rows(h0, h4) (network.rs:210) is split-K: the PE tile (K = 64) and h4 (K = 256) accumulate into
 //     the same D.  concat_rows(bottleneck, PE4(dir)) (network.rs:220) likewise (K = 256 + 32).
 //   - sigma (256 -> 1) and rgb (128 -> 3) heads are f32 dot products in the epilogue on the f32 accumulators.
 // Warp roles (both CTAs): warps 0..15 = epilogue (warp % 4 = TMEM lane quadrant, warp / 4 = column quarter; all
 // sixteen drain slot X's and slot Y's accumulators alternately), warp 16 = TMA producer of the CTA's weight halves,
 // warp 17 = MMA issuer (leader CTA only, one elected lane), warp 18 = TMEM allocator, warp 19 = relay ("my half of
-// chunk g has landed" -> leader).  The control warps have the highest warp ids because the warp schedulers pick
-// the highest eligible warp id first.
+// chunk g has landed" -> leader).  The control warps have the highest warp ids (measured placement-neutral, DESIGN.md
+// 4.1); setmaxnreg gives them 32 registers and the epilogue warps 112.
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
@@ -40,8 +40,8 @@ namespace nerf {
 namespace {
 
 constexpr int kThreads = 640;  // 16 epilogue warps + 4 control warps
-// The SM's warp schedulers favour the highest warp id among eligible warps, so the control warps sit above the
-// epilogue warps: an MMA issue, a TMA launch or a relay signal never queues behind conversion arithmetic.
+// The control warps sit above the epilogue warps (one setmaxnreg warp group of their own); their position among the
+// warp ids measured neutral for issue latency (scripts/sched_probe.cu).
 constexpr int kEpiWarps = 16, kWarpTma = 16, kWarpMma = 17, kWarpAlloc = 18, kWarpRelay = 19;
 constexpr int kStages = 4;
 constexpr uint32_t kStageBytes = 128 * 128;      // this CTA's N-half of a chunk: [128 x 64] 16-bit
