@@ -491,3 +491,32 @@ def test_other_weights_from_tensors_directory_and_cache(cam, ocam, tmp_path):
     finally:
         for r in rs:
             r.close()
+
+
+def test_forward_batch_million_samples(renderer, onets, ocam):
+    """SURVEY.md T3 at full size: 2^20 random in-volume samples through the fine network (1.2e12 FLOP on the oracle,
+    spread over the host cores in 2 048-sample slices), every mode against the same oracle values."""
+    import os
+    from concurrent.futures import ThreadPoolExecutor
+    n = 1 << 20
+    pts, dirs = _random_samples(ocam, n, seed=99)
+
+    def oracle_slice(k):
+        s = slice(k * 2048, (k + 1) * 2048)
+        return onets[1].forward_batch(np.ascontiguousarray(pts[:, s]), dirs[s])
+
+    with ThreadPoolExecutor(os.cpu_count() or 8) as ex:
+        outs = list(ex.map(oracle_slice, range(n // 2048)))
+    rgb_ref = np.concatenate([o[0] for o in outs])
+    sig_ref = np.concatenate([o[1] for o in outs])
+    assert sig_ref.max() > 300.0  # the sample set reaches the dense parts of the scene
+    for prec in ("fp32", "fp16x3", "fp16", "bf16"):
+        rgb, sig = renderer.fine.forward_batch(pts, dirs, precision=prec)
+        # the single-pass modes' maximum sits on isolated samples at a ReLU knee and grows with the sample count
+        # (fp16: 0.12 here against 0.04 over 4 000 samples); their bulk (99th percentile) is held to the usual bound
+        wide = prec in ("fp16", "bf16")
+        _check(prec, rgb, sig, rgb_ref, sig_ref, scale=4.0 if wide else 1.0)
+        ds = np.abs(sig - sig_ref) / np.maximum(1.0, np.abs(sig_ref))
+        assert np.percentile(ds, 99) <= SIG_P99[prec], (prec, float(np.percentile(ds, 99)))
+        if prec == "fp16x3":  # absolute, at densities up to ~1 000: the mode's f32-class claim
+            assert np.abs(sig - sig_ref).max() <= 4e-3 and np.abs(rgb - rgb_ref).max() <= 1e-4
