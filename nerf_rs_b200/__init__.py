@@ -158,26 +158,33 @@ def build_weight_cache(weights_root, cache_path):
     _check(lib().nerf_build_weight_cache(os.fsencode(weights_root), os.fsencode(cache_path)))
 
 
-def orbit_cameras(json_path, n_views):
-    """Synthetic poses of the throughput sweep: the JSON camera's radius and elevation,
-    azimuth theta_k = theta_0 + 2 pi k / n_views about +z (pose 0 is the JSON camera), forward = -pos / |pos| (the JSON
-    camera looks exactly at the origin), up = +z orthogonalised against forward, same near / far / hwf.  Each pose
-    goes through camera_from_samples (src/lib.rs:614-645) like the reference's own camera."""
+def orbit_poses(json_path, n_views):
+    """Synthetic poses of the throughput sweep as dicts with the reference's JSON keys: the
+    JSON camera's radius and elevation, azimuth theta_k = theta_0 + 2 pi k / n_views about +z (pose 0 is the JSON
+    camera), forward = -pos / |pos| (the JSON camera looks exactly at the origin), up = +z orthogonalised against
+    forward, same near / far / hwf."""
     import json
     with open(json_path) as f:
         d = json.load(f)
     o = np.array(d["camera_origin"], np.float64)
     radius, rho = float(np.linalg.norm(o)), float(np.hypot(o[0], o[1]))
     theta0 = float(np.arctan2(o[1], o[0]))
-    cams = []
+    poses = []
     for k in range(n_views):
         th = theta0 + 2.0 * np.pi * k / n_views
         pos = np.array([rho * np.cos(th), rho * np.sin(th), o[2]])
         fwd = -pos / radius
         up = np.array([0.0, 0.0, 1.0]) - fwd[2] * fwd
         up /= np.linalg.norm(up)
-        cams.append(camera_from_values(d["near"], d["far"], pos, fwd, up, d["hwf"]))
-    return cams
+        poses.append({"near": d["near"], "far": d["far"], "camera_origin": pos.tolist(), "camera_forward": fwd.tolist(),
+                      "camera_up": up.tolist(), "hwf": d["hwf"]})
+    return poses
+
+
+def orbit_cameras(json_path, n_views):
+    """orbit_poses through camera_from_samples (src/lib.rs:614-645), like the reference's own camera."""
+    return [camera_from_values(p["near"], p["far"], p["camera_origin"], p["camera_forward"], p["camera_up"], p["hwf"])
+            for p in orbit_poses(json_path, n_views)]
 
 
 def save_ppm(path, W, H, rgb):
