@@ -210,6 +210,21 @@ def test_cli_builds_and_fails_loudly_without_gpu(tmp_path):
     assert r.returncode != 0 and "no CPU fallback" in r.stderr and not (tmp_path / "o.ppm").exists()
 
 
+def test_cpp_mirror_builds_and_panics_without_gpu():
+    """include/nerf_rs.hpp (the reference crate's API over the C ABI) compiles into the reference's unit test
+    (tests/cpp/reference_examples.cpp); without a GPU load_network_from_dir panics - exit code 2, no fallback."""
+    import subprocess
+    import nerf_rs_b200 as nb
+    from tests.conftest import _have_gpu
+    exe = os.path.join(os.path.dirname(nb.LIB_PATH), "reference_examples")
+    assert os.path.exists(exe)
+    if not _have_gpu():
+        r = subprocess.run([exe, DATA], capture_output=True, text=True)
+        assert r.returncode == 2 and "no CPU fallback" in r.stderr
+    r = subprocess.run([exe, "/nonexistent"], capture_output=True, text=True)
+    assert r.returncode == 2 and "panic:" in r.stderr
+
+
 def test_integrate_aux_closed_form():
     """Constant sigma on a uniform grid: T_i = exp(-sigma * i * d), acc = 1 - exp(-sigma * L) up to the T < 1e-4
     cut-off of compute_weights (lib.rs:276-279), depth = sum w_i t_i by direct summation."""
