@@ -1,13 +1,19 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark: lego 800x800, 64 coarse + 128 fine samples/ray, rays/s.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--precision fp16|bf16|mixed|fp16x3|fp32] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--precision mixed|fp16|bf16|fp16x3|fp32] [--impl reference]
+                  [--gather peer|nccl] [--orbit VIEWS --res R] [--no-cpu]
 
 A step = one full 800x800 frame (640 000 rays, 163.84 M MLP samples) through the whole hot path
 (ray gen -> stratified -> coarse MLP -> importance resampling -> fine MLP -> compositing).
 `value` times it with the frame buffer resident in HBM (nerf_render_device); `e2e` times the public host API
 (pinned host output, D2H inside the timed region).  With N > 1 (torchrun) the frame is split into N contiguous
-pixel-index ranges, one per rank, and gathered to rank 0 over NCCL inside the timed region (strong scaling).
+pixel-index ranges, one per rank, and assembled on rank 0 inside the timed region (strong scaling): by default every
+rank's compositing kernel stores its rows straight into rank 0's frame buffer over NVLink (`--gather peer`, CUDA IPC
+mapping), `--gather nccl` uses one group of NCCL point-to-point transfers instead.  The default precision is `mixed`
+(coarse network split-fp16 x3, fine network fp16: the fastest mode whose frame stays within 2/255 of the f32 frame);
+the all-fp16 frame rate is reported beside it.  `--orbit V --res R` runs the multi-pose sweep (BASELINE.json
+configs[4]) instead.
 `--impl reference` times the reference's CPU algorithm (the oracle restatement; the Rust crate cannot be built
 here) on the host cores on a bounded ray sample of the same frame.
 """
