@@ -204,12 +204,24 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) importance_kernel(
       if (lane == 0) s_cdf[m] = 1.0f;  // lib.rs:327
       __syncwarp();
       const int64_t pixel = ray_begin + ray;
+      if (mode == NERF_SAMPLING_PHILOX) {
+        // one Philox4x32-10 block yields four consecutive uniforms (philox_uniform: block k / 4, element k % 4): evaluate
+        // each block once and park the uniforms in s_f, which the loop below overwrites element by element
+        for (int b = lane; 4 * b < nf; b += 32) {
+          uint32_t c[4] = {(uint32_t)pixel, (uint32_t)b, 1u, 0u};
+          philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (4 * b + j < nf) s_f[4 * b + j] = (float)(c[j] >> 8) * (1.0f / 16777216.0f);
+        }
+        __syncwarp();
+      }
       for (int k = lane; k < pf; k += 32) {
         float v = __int_as_float(0x7f800000);  // +inf padding for the sort
         if (k < nf) {
           float uu;
           if (mode == NERF_SAMPLING_DET) uu = ((float)k + 0.5f) / (float)nf;
-          else if (mode == NERF_SAMPLING_PHILOX) uu = philox_uniform(seed, (uint32_t)pixel, 1u, k);
+          else if (mode == NERF_SAMPLING_PHILOX) uu = s_f[k];  // == philox_uniform(seed, pixel, 1, k)
           else uu = u_in[ray * nf + k];
           // lib.rs:333-339 picks the first j with cdf[j] <= u < cdf[j+1], default m - 1.  By induction the first j with
           // u < cdf[j+1] already satisfies cdf[j] <= u, so idx = min{j : u < cdf[j+1]}; cdf[1..m-1] is a running sum of
