@@ -260,6 +260,10 @@ def gpu_arm(args):
     clocks = ClockSampler(local) if rank == 0 else None
     total_ms, (mc, mf, sm_ms, cp_ms) = timed(step_device, args.steps, True)
     clk = clocks.stop() if clocks else {}
+    stages_all = [[mc, mf, sm_ms, cp_ms]]
+    if world > 1:  # every rank's mean stage times, for the record (which rank bounds the frame, and in which kernel)
+        stages_all = [None] * world
+        dist.all_gather_object(stages_all, [mc, mf, sm_ms, cp_ms])
     fast_ms = None
     if args.precision == "mixed":  # the same frame with both networks in single-pass fp16, reported beside the headline
         step_device("fp16")
@@ -302,6 +306,7 @@ def gpu_arm(args):
             "samples_per_s": value * (NC + NC + NF),
             "tflops_frame": n_rays * (NC * FLOP_COARSE + (NC + NF) * FLOP_FINE) / (ms * 1e-3) / 1e12 ,
             "stage_ms_rank0": {"mlp_coarse": mc, "mlp_fine": mf, "sampling": sm_ms, "composite": cp_ms},
+            "stage_ms_by_rank": [[round(x, 3) for x in st] for st in stages_all],  # [coarse, fine, sampling, composite]
             "gpu_launches": 5 * args.steps,
             "clocks": clk,
             "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": h2d_bytes,
