@@ -9,8 +9,8 @@ A step = one full 800x800 frame (640 000 rays, 163.84 M MLP samples) through the
 `value` times it with the frame buffer resident in HBM (nerf_render_device); `e2e` times the public host API
 (pinned host output, D2H inside the timed region).  With N > 1 (torchrun) the frame is split into N contiguous
 pixel-index ranges, one per rank, and assembled on rank 0 inside the timed region (strong scaling): by default every
-rank's compositing kernel stores its rows straight into rank 0's frame buffer over NVLink (`--gather peer`, CUDA IPC
-mapping), `--gather nccl` uses one group of NCCL point-to-point transfers instead.  The default precision is `mixed`
+rank's compositing kernel stores its rows straight into rank 0's frame buffer over NVLink (`--gather peer`, buffer
+shared through the CUDA virtual-memory API), `--gather nccl` uses one group of NCCL point-to-point transfers instead.  The default precision is `mixed`
 (coarse network split-fp16 x3, fine network fp16: the fastest mode whose frame stays within 2/255 of the f32 frame);
 the all-fp16 frame rate is reported beside it.  `--orbit V --res R` runs the multi-pose sweep (BASELINE.json
 configs[4]) instead.
@@ -174,7 +174,8 @@ def gpu_arm(args):
     use_peer = world > 1 and args.gather == "peer"
     sf = None
     if use_peer:
-        # the frame lives in rank 0's HBM; every rank maps it (CUDA IPC) and its compositing kernel stores there
+        # the frame lives in rank 0's HBM; every rank maps it (VMM handle passed as a file descriptor) and its compositing
+        # kernel stores there
         try:
             sf = shard.SharedFrame(r, n_rays, rank, world, dist)
             ok = 1
@@ -301,7 +302,8 @@ def gpu_arm(args):
                        "l2": "flushed (256 MiB memset, untimed) before every step; per-frame intermediates ~3 GB >> 126 MB L2",
                        "gather": ("none" if world == 1 else
                                   "peer stores: every rank's compositing kernel writes its rows into rank 0's frame buffer over "
-                                  "NVLink (CUDA IPC mapping), inside the timed region; no collective on the data path" if use_peer else
+                                  "NVLink (the buffer is shared per allocation through the CUDA virtual-memory API), inside the timed region; "
+                                  "no collective on the data path" if use_peer else
                                   "NCCL point-to-point group: every rank sends its rgb range to rank 0, inside the timed region")},
             "samples_per_s": value * (NC + NC + NF),
             "tflops_frame": n_rays * (NC * FLOP_COARSE + (NC + NF) * FLOP_FINE) / (ms * 1e-3) / 1e12 ,

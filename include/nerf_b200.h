@@ -188,6 +188,15 @@ int nerf_shared_frame_create(nerf_ctx*, uint64_t bytes, void** d_ptr, unsigned c
 int nerf_shared_frame_open(nerf_ctx*, const unsigned char handle[NERF_IPC_HANDLE_BYTES], void** d_ptr);
 int nerf_shared_frame_close(nerf_ctx*, void* d_ptr, int owner);
 
+/* The same frame buffer shared per allocation through the CUDA virtual-memory API instead: only this buffer is mapped
+ * on the peers.  (The IPC form above turns on device-wide peer access, after which every allocation of the process is
+ * mapped for the peer - measured to cost the MLP kernels 1-3 %.)  create returns the mapped size and a POSIX file
+ * descriptor to hand to the other ranks (SCM_RIGHTS over a Unix socket; the caller closes its copy), open maps the
+ * received descriptor, close_fd unmaps and drops this process's reference (the memory is freed with the last one). */
+int nerf_shared_frame_create_fd(nerf_ctx*, uint64_t bytes, void** d_ptr, uint64_t* mapped_bytes, int* fd);
+int nerf_shared_frame_open_fd(nerf_ctx*, int fd, uint64_t mapped_bytes, void** d_ptr);
+int nerf_shared_frame_close_fd(nerf_ctx*, void* d_ptr);
+
 /* Stage entry points (host buffers), one per reference function, used by the stage-wise parity tests. */
 int nerf_ray_dirs(nerf_ctx*, const nerf_camera*, int W, int H, int64_t ray_begin, int64_t ray_end,
                   float* dirs /*[n][3]*/);                                   /* lib.rs:214-230 + :371 */

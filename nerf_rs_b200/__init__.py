@@ -32,7 +32,8 @@ EXPORTS = ["nerf_last_error", "nerf_version", "nerf_create", "nerf_create_from_t
            "nerf_integrate_rays", "nerf_get_timing", "nerf_camera_from_json", "nerf_camera_from_values",
            "nerf_save_ppm", "nerf_quantize_rgb8", "nerf_render_rgb8", "nerf_render_rgb8_device", "nerf_render_many",
            "nerf_quantize_rgb8_gpu", "nerf_render_aux", "nerf_render_aux_device", "nerf_build_weight_cache",
-           "nerf_create_from_cache", "nerf_shared_frame_create", "nerf_shared_frame_open", "nerf_shared_frame_close"]
+           "nerf_create_from_cache", "nerf_shared_frame_create", "nerf_shared_frame_open", "nerf_shared_frame_close",
+           "nerf_shared_frame_create_fd", "nerf_shared_frame_open_fd", "nerf_shared_frame_close_fd"]
 
 
 E_ARG, E_IO, E_SHAPE, E_CUDA, E_UNSUPPORTED = -1, -2, -3, -4, -5  # nerf_status
@@ -92,6 +93,9 @@ def lib():
     L.nerf_shared_frame_create.argtypes = [vp, C.c_uint64, C.POINTER(vp), C.c_char_p]
     L.nerf_shared_frame_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
     L.nerf_shared_frame_close.argtypes = [vp, vp, i32]
+    L.nerf_shared_frame_create_fd.argtypes = [vp, C.c_uint64, C.POINTER(vp), C.POINTER(C.c_uint64), C.POINTER(i32)]
+    L.nerf_shared_frame_open_fd.argtypes = [vp, i32, C.c_uint64, C.POINTER(vp)]
+    L.nerf_shared_frame_close_fd.argtypes = [vp, vp]
     L.nerf_build_weight_cache.argtypes = [C.c_char_p, C.c_char_p]
     L.nerf_create_from_cache.argtypes = [C.c_char_p, i32, C.POINTER(vp)]
     L.nerf_create_from_tensors.argtypes = [C.POINTER(Tensor), i32, C.POINTER(Tensor), i32, i32, C.POINTER(vp)]

@@ -7,6 +7,11 @@
 #include <new>
 #include <vector>
 
+#include <cuda.h>  // types only: the driver entry points are fetched with cudaGetDriverEntryPoint, libcuda is not linked
+#include <unistd.h>
+
+#include <map>
+
 #include "common.cuh"
 #include "host_util.h"
 #include "mlp_tc.h"
@@ -81,6 +86,8 @@ struct nerf_ctx {
   bool have_timing = false;
   int launches = 0;
   int64_t chunk_rays = 1 << 20;
+  struct VmmFrame { CUmemGenericAllocationHandle handle; size_t size; };
+  std::map<void*, VmmFrame> vmm_frames;  // nerf_shared_frame_*_fd mappings owned by this context
 };
 
 namespace nerf {
@@ -362,6 +369,90 @@ void timing_start(nerf_ctx* c, cudaStream_t s) {
 }
 void timing_stop(nerf_ctx* c, cudaStream_t s) { cudaEventRecord(c->ev_end, s); }
 
+}  // namespace
+}  // namespace nerf
+
+// ---- per-allocation sharing through the CUDA virtual-memory API (driver entry points, resolved at run time)
+namespace nerf {
+namespace {
+struct VmmApi {
+  decltype(&cuMemGetAllocationGranularity) granularity = nullptr;
+  decltype(&cuMemCreate) create = nullptr;
+  decltype(&cuMemRelease) release = nullptr;
+  decltype(&cuMemAddressReserve) reserve = nullptr;
+  decltype(&cuMemAddressFree) addr_free = nullptr;
+  decltype(&cuMemMap) map = nullptr;
+  decltype(&cuMemUnmap) unmap = nullptr;
+  decltype(&cuMemSetAccess) set_access = nullptr;
+  decltype(&cuMemExportToShareableHandle) export_handle = nullptr;
+  decltype(&cuMemImportFromShareableHandle) import_handle = nullptr;
+  bool ok = false;
+};
+const VmmApi& vmm_api() {
+  static const VmmApi api = [] {
+    VmmApi a;
+    bool ok = true;
+    auto get = [&](const char* name, void** fn) {
+      cudaDriverEntryPointQueryResult st;
+      if (cudaGetDriverEntryPoint(name, fn, cudaEnableDefault, &st) != cudaSuccess || st != cudaDriverEntryPointSuccess ||
+          *fn == nullptr)
+        ok = false;
+    };
+    get("cuMemGetAllocationGranularity", (void**)&a.granularity);
+    get("cuMemCreate", (void**)&a.create);
+    get("cuMemRelease", (void**)&a.release);
+    get("cuMemAddressReserve", (void**)&a.reserve);
+    get("cuMemAddressFree", (void**)&a.addr_free);
+    get("cuMemMap", (void**)&a.map);
+    get("cuMemUnmap", (void**)&a.unmap);
+    get("cuMemSetAccess", (void**)&a.set_access);
+    get("cuMemExportToShareableHandle", (void**)&a.export_handle);
+    get("cuMemImportFromShareableHandle", (void**)&a.import_handle);
+    a.ok = ok;
+    return a;
+  }();
+  return api;
+}
+CUmemAllocationProp frame_prop(int owner_device) {
+  CUmemAllocationProp prop{};
+  prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+  prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  prop.location.id = owner_device;
+  prop.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  return prop;
+}
+#define NERF_CU(expr)                                                                \
+  do {                                                                               \
+    CUresult _r = (expr);                                                            \
+    if (_r != CUDA_SUCCESS) {                                                        \
+      set_error(std::string(#expr) + ": CUresult " + std::to_string((int)_r));       \
+      return NERF_E_CUDA;                                                            \
+    }                                                                                \
+  } while (0)
+
+// Reserves an address range, maps `handle` there and gives this context's device read/write access.
+int vmm_map(nerf_ctx* c, CUmemGenericAllocationHandle handle, size_t size, void** out) {
+  const VmmApi& a = vmm_api();
+  CUdeviceptr va = 0;
+  NERF_CU(a.reserve(&va, size, 0, 0, 0));
+  CUresult r = a.map(va, size, 0, handle, 0);
+  if (r == CUDA_SUCCESS) {
+    CUmemAccessDesc acc{};
+    acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    acc.location.id = c->device;
+    acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+    r = a.set_access(va, size, &acc, 1);
+    if (r != CUDA_SUCCESS) a.unmap(va, size);
+  }
+  if (r != CUDA_SUCCESS) {
+    a.addr_free(va, size);
+    set_error("map shared frame: CUresult " + std::to_string((int)r));
+    return NERF_E_CUDA;
+  }
+  *out = reinterpret_cast<void*>(va);
+  c->vmm_frames[*out] = nerf_ctx::VmmFrame{handle, size};
+  return NERF_OK;
+}
 }  // namespace
 }  // namespace nerf
 
@@ -956,6 +1047,82 @@ int nerf_shared_frame_close(nerf_ctx* c, void* d_ptr, int owner) {
   NERF_CUDA(cudaDeviceSynchronize());
   if (owner) NERF_CUDA(cudaFree(d_ptr));
   else NERF_CUDA(cudaIpcCloseMemHandle(d_ptr));
+  return NERF_OK;
+}
+
+int nerf_shared_frame_create_fd(nerf_ctx* c, uint64_t bytes, void** d_ptr, uint64_t* mapped_bytes, int* fd) {
+  if (!c || !d_ptr || !mapped_bytes || !fd || bytes == 0) {
+    set_error("nerf_shared_frame_create_fd: bad argument");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  NERF_CUDA(cudaFree(nullptr));  // make sure the primary context exists
+  const VmmApi& a = vmm_api();
+  if (!a.ok) {
+    set_error("CUDA virtual-memory entry points unavailable");
+    return NERF_E_UNSUPPORTED;
+  }
+  const CUmemAllocationProp prop = frame_prop(c->device);
+  size_t gran = 0;
+  NERF_CU(a.granularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
+  const size_t size = (bytes + gran - 1) / gran * gran;
+  CUmemGenericAllocationHandle h;
+  NERF_CU(a.create(&h, size, &prop, 0));
+  int out_fd = -1;
+  CUresult r = a.export_handle(&out_fd, h, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
+  if (r != CUDA_SUCCESS) {
+    a.release(h);
+    set_error("cuMemExportToShareableHandle: CUresult " + std::to_string((int)r));
+    return NERF_E_CUDA;
+  }
+  int rc = vmm_map(c, h, size, d_ptr);
+  if (rc != NERF_OK) {
+    ::close(out_fd);
+    a.release(h);
+    return rc;
+  }
+  *mapped_bytes = size;
+  *fd = out_fd;
+  return NERF_OK;
+}
+
+int nerf_shared_frame_open_fd(nerf_ctx* c, int fd, uint64_t mapped_bytes, void** d_ptr) {
+  if (!c || !d_ptr || fd < 0 || mapped_bytes == 0) {
+    set_error("nerf_shared_frame_open_fd: bad argument");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  NERF_CUDA(cudaFree(nullptr));
+  const VmmApi& a = vmm_api();
+  if (!a.ok) {
+    set_error("CUDA virtual-memory entry points unavailable");
+    return NERF_E_UNSUPPORTED;
+  }
+  CUmemGenericAllocationHandle h;
+  NERF_CU(a.import_handle(&h, (void*)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
+  int rc = vmm_map(c, h, (size_t)mapped_bytes, d_ptr);
+  if (rc != NERF_OK) a.release(h);
+  return rc;
+}
+
+int nerf_shared_frame_close_fd(nerf_ctx* c, void* d_ptr) {
+  if (!c || !d_ptr) return NERF_OK;
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  auto it = c->vmm_frames.find(d_ptr);
+  if (it == c->vmm_frames.end()) {
+    set_error("nerf_shared_frame_close_fd: not a frame of this context");
+    return NERF_E_ARG;
+  }
+  NERF_CUDA(cudaDeviceSynchronize());
+  const VmmApi& a = vmm_api();
+  const CUdeviceptr va = reinterpret_cast<CUdeviceptr>(d_ptr);
+  NERF_CU(a.unmap(va, it->second.size));
+  NERF_CU(a.addr_free(va, it->second.size));
+  NERF_CU(a.release(it->second.handle));  // the memory goes away with the last mapping / handle, in whichever process
+  c->vmm_frames.erase(it);
   return NERF_OK;
 }
 

@@ -41,18 +41,26 @@ def gather_frame(local, frame, rank, world, dist=None, group=None):
 
 
 class SharedFrame:
-    """The frame buffer of a multi-GPU render, in rank 0's HBM, mapped into every rank through CUDA IPC
-    (nerf_shared_frame_*): each rank renders its ray range with `d_rgb = frame.row_ptr(ray_begin)`, so the compositing
-    kernel's stores go straight to rank 0 over NVLink and no collective moves pixels.  `complete()` is the only
-    synchronisation: every rank drains its stream, then a barrier."""
+    """The frame buffer of a multi-GPU render, in rank 0's HBM, mapped into every rank: each rank renders its ray range
+    with `d_rgb = frame.row_ptr(ray_begin)`, so the compositing kernel's stores go straight to rank 0 over NVLink and no
+    collective moves pixels.  `complete()` is the only synchronisation: every rank drains its stream, then a barrier.
 
-    def __init__(self, renderer, n_rays, rank, world, dist=None, group=None, channels=3, itemsize=4):
+    how = "vmm" (default): the buffer alone is shared, through the CUDA virtual-memory API
+    (nerf_shared_frame_*_fd); rank 0 hands its file descriptor to each rank over a Unix socket (SCM_RIGHTS).
+    how = "ipc": cudaIpc handles (nerf_shared_frame_create / open); simpler, but opening one turns on device-wide peer
+    access, which was measured to slow the MLP kernels of every rank by 1-3 %."""
+
+    def __init__(self, renderer, n_rays, rank, world, dist=None, group=None, channels=3, itemsize=4, how="vmm"):
         import ctypes as C
         from . import _check, lib
         self.renderer, self.rank, self.world, self.dist, self.group = renderer, rank, world, dist, group
         self.n_rays, self.row_bytes = n_rays, channels * itemsize
-        self.channels = channels
+        self.channels, self.how = channels, how
         ptr = C.c_void_p()
+        if how == "vmm":
+            self.ptr = self._init_vmm(ptr)
+            self.handle = None
+            return
         handle, err = [None], None
         if rank == 0:
             buf = C.create_string_buffer(64)
@@ -69,6 +77,58 @@ class SharedFrame:
             _check(lib().nerf_shared_frame_open(renderer._h, handle[0], C.byref(ptr)))
         self.handle = handle[0]
         self.ptr = ptr.value
+
+    def _init_vmm(self, ptr):
+        """Rank 0 creates the allocation and serves its file descriptor on a Unix socket; the others connect, receive
+        it (SCM_RIGHTS) and map it.  The socket path and the mapped size travel through broadcast_object_list."""
+        import ctypes as C
+        import os
+        import socket
+        import tempfile
+        from . import _check, lib
+        L, h = lib(), self.renderer._h
+        info, srv, fd = [None], None, -1
+        if self.rank == 0:
+            size, cfd = C.c_uint64(), C.c_int(-1)
+            rc = L.nerf_shared_frame_create_fd(h, self.n_rays * self.row_bytes, C.byref(ptr), C.byref(size), C.byref(cfd))
+            if rc == 0:
+                fd = cfd.value
+                path = None
+                if self.world > 1:
+                    path = os.path.join(tempfile.mkdtemp(prefix="nerf_frame_"), "fd.sock")
+                    srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                    srv.bind(path)
+                    srv.listen(self.world)
+                info = [(path, size.value)]
+            else:
+                info = [("error: " + L.nerf_last_error().decode(), 0)]
+        if self.world > 1:
+            self.dist.broadcast_object_list(info, src=0, group=self.group)
+        path, size = info[0]
+        if size == 0:
+            raise RuntimeError("shared frame: rank 0 could not create it (" + str(path) + ")")
+        if self.rank == 0:
+            try:
+                for _ in range(self.world - 1):
+                    conn, _ = srv.accept()
+                    socket.send_fds(conn, [b"f"], [fd])
+                    conn.close()
+            finally:
+                if srv is not None:
+                    srv.close()
+                    os.unlink(path)
+                    os.rmdir(os.path.dirname(path))
+                os.close(fd)  # the mapping keeps the allocation alive
+        else:
+            cli = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            cli.connect(path)
+            _, fds, _, _ = socket.recv_fds(cli, 16, 1)
+            cli.close()
+            try:
+                _check(L.nerf_shared_frame_open_fd(h, fds[0], size, C.byref(ptr)))
+            finally:
+                os.close(fds[0])
+        return ptr.value
 
     def row_ptr(self, ray):
         return self.ptr + ray * self.row_bytes
@@ -94,5 +154,8 @@ class SharedFrame:
     def close(self):
         from . import _check, lib
         if self.ptr:
-            _check(lib().nerf_shared_frame_close(self.renderer._h, self.ptr, 1 if self.rank == 0 else 0))
+            if self.how == "vmm":
+                _check(lib().nerf_shared_frame_close_fd(self.renderer._h, self.ptr))
+            else:
+                _check(lib().nerf_shared_frame_close(self.renderer._h, self.ptr, 1 if self.rank == 0 else 0))
             self.ptr = 0

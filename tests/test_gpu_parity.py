@@ -417,7 +417,7 @@ def test_shared_frame_second_process_stores_into_the_owner_buffer(renderer, cam)
     from tests.conftest import ROOT
     W, H = 48, 40
     n = W * H
-    sf = shard.SharedFrame(renderer, n, 0, 1)
+    sf = shard.SharedFrame(renderer, n, 0, 1, how="ipc")
     try:
         assert len(sf.handle) == 64 and sf.ptr
         frame = sf.tensor()
@@ -541,3 +541,61 @@ def test_reference_unit_test_through_the_cpp_mirror(renderer, cam, tmp_path, pre
         assert "sigma" in r.stdout and " rgb" not in r.stdout  # only densities miss the bound
     img = renderer.render_image(cam, 32, 24, 64, 128, precision=prec)
     assert out.read_bytes() == b"P6\n32 24\n255\n" + nb.quantize_rgb8(img).tobytes()
+
+
+_VMM_CHILD = r"""
+import sys, ctypes as C
+sys.path.insert(0, sys.argv[1])
+import nerf_rs_b200 as nb
+fd, size, W, H, rb, re_ = (int(x) for x in sys.argv[2:8])
+r = nb.Renderer(nb.DATA_ROOT, device=0)
+cam = nb.camera_from_json(nb.DATA_ROOT + "/tf_reference_samples.json")
+p = C.c_void_p()
+assert nb.lib().nerf_shared_frame_open_fd(r._h, fd, size, C.byref(p)) == 0, nb.lib().nerf_last_error()
+r.render_device(cam, W, H, p.value + 12 * rb, 64, 128, precision="mixed", ray_begin=rb, ray_end=re_)
+import torch
+torch.cuda.synchronize()
+assert nb.lib().nerf_shared_frame_close_fd(r._h, p) == 0
+r.close()
+print("child ok")
+"""
+
+
+def test_shared_frame_per_allocation_mapping(renderer, cam):
+    """The same assembly with the frame buffer shared through the CUDA virtual-memory API (nerf_shared_frame_*_fd, what
+    shard.SharedFrame and bench.py use by default): rank 0 exports a file descriptor, the second process maps it and
+    stores its ray range; no device-wide peer access is involved."""
+    import ctypes as C
+    import os
+    import subprocess
+    import sys
+    import torch
+    from nerf_rs_b200 import shard
+    from tests.conftest import ROOT
+    W, H = 48, 40
+    n = W * H
+    L = nb.lib()
+    ptr, size, fd = C.c_void_p(), C.c_uint64(), C.c_int(-1)
+    assert L.nerf_shared_frame_create_fd(renderer._h, n * 12, C.byref(ptr), C.byref(size), C.byref(fd)) == 0, L.nerf_last_error()
+    try:
+        assert size.value >= n * 12 and fd.value >= 0
+        half = shard.ray_range(1, 2, n)[0]
+        child = subprocess.run([sys.executable, "-c", _VMM_CHILD, ROOT, str(fd.value), str(size.value), str(W), str(H),
+                                str(half), str(n)], capture_output=True, text=True, timeout=300, pass_fds=(fd.value,))
+        assert child.returncode == 0 and "child ok" in child.stdout, child.stderr[-2000:]
+        renderer.render_device(cam, W, H, ptr.value, 64, 128, precision="mixed", ray_begin=0, ray_end=half)
+        torch.cuda.synchronize()
+        class _Raw:
+            __cuda_array_interface__ = {"shape": (n, 3), "typestr": "<f4", "data": (ptr.value, False), "version": 2}
+        got = torch.as_tensor(_Raw(), device="cuda:0").cpu().numpy()
+        want = renderer.render_image(cam, W, H, 64, 128, precision="mixed")
+        assert (got == want).all()
+        # the helper the bench uses: single rank, creates and maps without a socket
+        sf = shard.SharedFrame(renderer, n, 0, 1)
+        t = sf.tensor()
+        t.zero_()
+        assert t.shape == (n, 3) and float(t.sum()) == 0.0
+        sf.close()
+    finally:
+        os.close(fd.value)
+        assert L.nerf_shared_frame_close_fd(renderer._h, ptr) == 0
