@@ -299,3 +299,19 @@ def test_weight_cache_file_is_deterministic_and_checked(tmp_path):
     from tests.conftest import _have_gpu
     if not _have_gpu():
         assert L.nerf_create_from_cache(os.fsencode(a), 0, C.byref(h)) == nb.E_CUDA
+
+
+def test_shared_frame_entry_points_reject_bad_arguments():
+    """The multi-GPU frame-buffer entry points (both forms) return NERF_E_ARG on null / empty arguments before touching
+    CUDA, so the check runs without a GPU; closing nothing is a no-op."""
+    import ctypes as C
+    import nerf_rs_b200 as nb
+    L = nb.lib()
+    p, size, fd, buf = C.c_void_p(), C.c_uint64(), C.c_int(-1), C.create_string_buffer(64)
+    assert L.nerf_shared_frame_create(None, 1024, C.byref(p), buf) == nb.E_ARG
+    assert L.nerf_shared_frame_open(None, buf, C.byref(p)) == nb.E_ARG
+    assert L.nerf_shared_frame_close(None, None, 1) == 0
+    assert L.nerf_shared_frame_create_fd(None, 1024, C.byref(p), C.byref(size), C.byref(fd)) == nb.E_ARG
+    assert L.nerf_shared_frame_open_fd(None, 3, 1024, C.byref(p)) == nb.E_ARG
+    assert L.nerf_shared_frame_close_fd(None, None) == 0
+    assert b"bad argument" in L.nerf_last_error()
