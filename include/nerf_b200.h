@@ -16,7 +16,9 @@
  *     sm_100 device is present.
  *   - "host" entry points take host pointers and include H2D/D2H copies; "*_device" entry points take
  *     device pointers on the context's device and enqueue on `stream` (a cudaStream_t passed as void*),
- *     returning without synchronising.
+ *     returning without synchronising.  A context has ONE set of workspaces: calls on different streams are ordered
+ *     on the device in the order they were enqueued (the next call's stream waits for an event the previous call
+ *     recorded), so they never overlap; use one context per stream for concurrency.
  */
 #ifndef NERF_B200_H
 #define NERF_B200_H
@@ -41,17 +43,23 @@ typedef enum {
 typedef enum {
   NERF_PREC_FP32 = 0, /* CUDA-core path; per-element sum order identical to network.rs:134-143 */
   NERF_PREC_BF16 = 1, /* tcgen05 kind::f16, bf16 operands, f32 accumulate in TMEM */
-  NERF_PREC_FP16 = 2, /* tcgen05 kind::f16, fp16 operands (tf32-class 10-bit mantissa at bf16 rate) */
-  NERF_PREC_TF32 = 3, /* served by the FP16 path (same 10-bit operand mantissa at twice the tf32 rate) */
+  NERF_PREC_FP16 = 2, /* tcgen05 kind::f16, fp16 operands: the 10-bit operand mantissa of tf32 at twice its rate.  This
+                       * is what serves the north star's "tf32 mode"; there is no kind::tf32 kernel. */
+  NERF_PREC_TF32 = 3, /* reserved, NOT a mode: every entry point answers NERF_E_UNSUPPORTED (round 1 silently ran the
+                       * FP16 path under this name).  Ask for NERF_PREC_FP16. */
   NERF_PREC_FP16X3 = 4 /* tcgen05 kind::f16, every operand split x = hi + lo (two fp16), three MMAs per product
                         * (hi.hi + lo.hi + hi.lo), f32 accumulate: ~22-bit operands, f32-class results at a third
                         * of the FP16 rate.  The mode that meets the reference-accuracy bounds on the tensor cores. */
   ,
-  NERF_PREC_MIXED = 5  /* coarse network FP16X3, fine network FP16.  The coarse densities only place the fine samples
-                        * (lib.rs:409-420), and where the coarse weights are almost zero the inverse CDF turns a 1e-4
-                        * weight error into a visible shift of a sample; on thin structures that is the whole
-                        * difference between an FP16 frame and the f32 one.  With f32-class coarse densities the
-                        * frame stays within 2/255 of the f32 frame at 2/3 of the FP16 frame rate. */
+  NERF_PREC_MIXED = 5  /* coarse network at FP16X3 accuracy, fine network FP16.  The coarse densities only place the
+                        * fine samples (lib.rs:409-420), and where the coarse weights are almost zero the inverse CDF
+                        * turns a 1e-4 weight error into a visible shift of a sample; on thin structures that is the
+                        * whole difference between an FP16 frame and the f32 one.  In a render the coarse pass is two
+                        * passes: FP16 over every sample, then FP16X3 over the samples whose density can reach a coarse
+                        * weight at all (pre-activation above -0.5 and transmittance in front of it above 6e-6; the
+                        * others are exactly zero or behind the reference's own T < 1e-4 cut-off, lib.rs:276-279) - the
+                        * frame is bit-identical to the one with FP16X3 over every coarse sample.  nerf_forward_batch
+                        * has no rays, so there MIXED means FP16X3 for the coarse network and FP16 for the fine one. */
 } nerf_precision;
 
 typedef enum { NERF_NET_COARSE = 0, NERF_NET_FINE = 1 } nerf_net_id;
@@ -112,6 +120,11 @@ typedef struct {
   float sampling_ms;   /* ray generation + stratified + importance sampling kernels */
   float composite_ms;  /* compositing kernel */
   int32_t kernel_launches;
+  /* mixed mode only (0 otherwise): the part of mlp_coarse_ms spent selecting and re-evaluating coarse samples with
+   * split operands, how many coarse samples the render had, and how many of them were re-evaluated */
+  float coarse_refine_ms;
+  int64_t coarse_samples;
+  int64_t coarse_refined;
 } nerf_timing;
 
 const char* nerf_last_error(void);

@@ -8,6 +8,8 @@
 //   reference (Rust)                                          here (C++)
 //   nerf_rs::vec3::Vec3 {x, y, z}            vec3.rs:3-47     nerf_rs::Vec3
 //   nerf_rs::network::Matrix                 network.rs:3-60  nerf_rs::Matrix      (row-major f32, dims i32)
+//   nerf_rs::network::Layer::new             network.rs:75    nerf_rs::Layer
+//   nerf_rs::network::Network::new           network.rs:181   nerf_rs::Network::create
 //   nerf_rs::network::Network::forward_batch network.rs:197   nerf_rs::Network::forward_batch
 //   load_network_from_dir(dir)               lib.rs:108-174   nerf_rs::load_network_from_dir
 //   Camera / camera_from_samples             lib.rs:197-211,614-645   nerf_rs::Camera / camera_from_samples
@@ -82,11 +84,50 @@ class Matrix {  // row-major; activations are [features x batch], a column is a 
   std::vector<float> data_;
 };
 
+// network.rs:62-78: a dense layer as the caller holds it - weight is [in x out] row-major (the file layout of
+// lego_rust/*/_kernel.bin), bias has `out` entries.  Host data only; the arithmetic happens on the GPU once the layers
+// are handed to Network::create.
+struct Layer {
+  Matrix weight;
+  std::vector<float> bias;
+  Layer(Matrix weight_, std::vector<float> bias_) : weight(std::move(weight_)), bias(std::move(bias_)) {  // Layer::new
+    if ((size_t)weight.cols() != bias.size()) throw Panic("Layer::new: bias length != weight.cols()");
+  }
+};
+
+// The tensors of one network in the order and under the names of shapes.txt (lib.rs:108-174).
+struct HostNet {
+  std::vector<Layer> layers;  // dense0..7, bottleneck, viewdirs, rgb, alpha
+  std::vector<std::string> names;
+  std::vector<nerf_tensor> tensors() const {
+    std::vector<nerf_tensor> t;
+    for (size_t i = 0; i < layers.size(); ++i) {
+      nerf_tensor k{}, b{};
+      k.name = names[2 * i].c_str();
+      k.ndim = 2;
+      k.dims[0] = layers[i].weight.rows();
+      k.dims[1] = layers[i].weight.cols();
+      k.data = layers[i].weight.data().data();
+      b.name = names[2 * i + 1].c_str();
+      b.ndim = 1;
+      b.dims[0] = (int64_t)layers[i].bias.size();
+      b.data = layers[i].bias.data();
+      t.push_back(k);
+      t.push_back(b);
+    }
+    return t;
+  }
+};
+
 // One GPU context per weight root (it holds both networks of a scene: a render needs both).
 class Context {
  public:
   Context(const std::string& root, int device) {
     check(nerf_create(root.c_str(), device, &ctx_), "load_network_from_dir");
+  }
+  Context(const HostNet& coarse, const HostNet& fine, int device) {  // Network::new (network.rs:181-195)
+    const std::vector<nerf_tensor> c = coarse.tensors(), f = fine.tensors();
+    check(nerf_create_from_tensors(c.data(), (int)c.size(), f.data(), (int)f.size(), device, &ctx_), "Network::new");
   }
   ~Context() { nerf_destroy(ctx_); }
   Context(const Context&) = delete;
@@ -100,9 +141,37 @@ class Context {
 class Network {
  public:
   Network(std::shared_ptr<Context> ctx, int net_id) : ctx_(std::move(ctx)), net_(net_id) {}
-  // Arithmetic of the 256-wide layers (nerf_precision); the default is the library's default.
+  // Network::new (network.rs:181-195): eight trunk layers, then bottleneck, viewdirs, rgb, alpha.  A GPU context
+  // always holds the two networks of a scene, so a network built on its own sits in both slots of its context; hand
+  // two of them to render_image and it builds (and keeps) the coarse + fine context of the pair.
+  static Network create(std::vector<Layer> layers, Layer bottleneck, Layer viewdirs, Layer rgb, Layer alpha,
+                        int device = 0) {
+    if (layers.size() != 8) throw Panic("Network::new: the trunk has eight layers (network.rs:206-213)");
+    auto host = std::make_shared<HostNet>();
+    host->layers = std::move(layers);
+    host->layers.push_back(std::move(bottleneck));
+    host->layers.push_back(std::move(viewdirs));
+    host->layers.push_back(std::move(rgb));
+    host->layers.push_back(std::move(alpha));
+    static const char* const stem[12] = {"dense0", "dense1", "dense2", "dense3", "dense4", "dense5",
+                                         "dense6", "dense7", "bottleneck", "viewdirs", "rgb", "alpha"};
+    for (const char* n : stem) {
+      host->names.push_back(std::string(n) + "_kernel");
+      host->names.push_back(std::string(n) + "_bias");
+    }
+    Network net(std::make_shared<Context>(*host, *host, device), NERF_NET_FINE);
+    net.host_ = std::move(host);
+    net.device_ = device;
+    return net;
+  }
+  const std::shared_ptr<HostNet>& host() const { return host_; }
+  int device() const { return device_; }
+  // Arithmetic of the 256-wide layers (nerf_precision).  Unset, forward_batch runs NERF_PREC_FP16X3 - the tensor-core
+  // mode that passes the reference's own unit test (1e-2 abs on sigma up to 213, lib.rs:732-742) with margin - and
+  // render_image runs NERF_PREC_MIXED, where the image bound is the criterion.
   void set_precision(int p) { precision_ = p; }
-  int precision() const { return precision_; }
+  int precision() const { return precision_ >= 0 ? precision_ : NERF_PREC_FP16X3; }
+  int render_precision() const { return precision_ >= 0 ? precision_ : NERF_PREC_MIXED; }
   const std::shared_ptr<Context>& context() const { return ctx_; }
   int net_id() const { return net_; }
 
@@ -115,7 +184,7 @@ class Network {
     std::vector<Vec3> rgb((size_t)batch);
     std::vector<float> sigma((size_t)batch);
     check(nerf_forward_batch(ctx_->get(), net_, points.data().data(), reinterpret_cast<const float*>(view_dirs.data()),
-                             batch, precision_, reinterpret_cast<float*>(rgb.data()), sigma.data()),
+                             batch, precision(), reinterpret_cast<float*>(rgb.data()), sigma.data()),
           "forward_batch");
     return {std::move(rgb), std::move(sigma)};
   }
@@ -123,7 +192,9 @@ class Network {
  private:
   std::shared_ptr<Context> ctx_;
   int net_;
-  int precision_ = NERF_PREC_MIXED;
+  int precision_ = -1;  // unset: see set_precision
+  std::shared_ptr<HostNet> host_;  // only for networks built from caller-held layers
+  int device_ = 0;
 };
 
 // lib.rs:108-174.  `dir` is <root>/coarse or <root>/fine, as the reference calls it (lib.rs:651-652); both calls share
@@ -169,14 +240,24 @@ inline Camera camera_from_samples(const std::string& json_path, size_t nx, size_
 // (default: Philox seed 0; NERF_SAMPLING_DET for the parity tests).
 inline std::vector<Vec3> render_image(const Network& coarse, const Network& fine, const Camera& cam,
                                       size_t fine_samples_per_ray, const nerf_sampling* sampling = nullptr) {
-  if (coarse.context() != fine.context() || coarse.net_id() != NERF_NET_COARSE || fine.net_id() != NERF_NET_FINE)
+  std::shared_ptr<Context> ctx = coarse.context();
+  if (coarse.host() && fine.host()) {
+    // two networks built with Network::create: the pair's own context, built once
+    static std::mutex mu;
+    static std::map<std::pair<const HostNet*, const HostNet*>, std::shared_ptr<Context>> pairs;
+    std::lock_guard<std::mutex> lk(mu);
+    std::shared_ptr<Context>& slot = pairs[{coarse.host().get(), fine.host().get()}];
+    if (!slot) slot = std::make_shared<Context>(*coarse.host(), *fine.host(), coarse.device());
+    ctx = slot;
+  } else if (coarse.context() != fine.context() || coarse.net_id() != NERF_NET_COARSE || fine.net_id() != NERF_NET_FINE) {
     throw Panic("render_image: coarse and fine must come from the same weight root");
+  }
   nerf_sampling smp{};
   smp.mode = NERF_SAMPLING_PHILOX;
   if (sampling) smp = *sampling;
   std::vector<Vec3> image(cam.nx * cam.ny);
-  check(nerf_render(coarse.context()->get(), &cam.c, (int)cam.nx, (int)cam.ny, (int)cam.samples_per_ray,
-                    (int)fine_samples_per_ray, fine.precision(), &smp, 0, (int64_t)(cam.nx * cam.ny),
+  check(nerf_render(ctx->get(), &cam.c, (int)cam.nx, (int)cam.ny, (int)cam.samples_per_ray,
+                    (int)fine_samples_per_ray, fine.render_precision(), &smp, 0, (int64_t)(cam.nx * cam.ny),
                     reinterpret_cast<float*>(image.data())),
         "render_image");  // W % 8, H % 8, samples == 0 -> the asserts of lib.rs:483-501
   return image;

@@ -19,7 +19,8 @@ LIB_PATH = os.path.join(_HERE, "libnerf_b200.so")
 DATA_ROOT = os.path.join(os.path.dirname(_HERE), "data", "lego_rust")
 
 PREC_FP32, PREC_BF16, PREC_FP16, PREC_TF32, PREC_FP16X3, PREC_MIXED = 0, 1, 2, 3, 4, 5
-PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "fp16": PREC_FP16, "tf32": PREC_TF32, "fp16x3": PREC_FP16X3, "mixed": PREC_MIXED}
+# PREC_TF32 is reserved by the ABI and answers E_UNSUPPORTED: there is no kind::tf32 kernel, fp16 serves that slot
+PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "fp16": PREC_FP16, "fp16x3": PREC_FP16X3, "mixed": PREC_MIXED}
 NET_COARSE, NET_FINE = 0, 1
 SAMPLING_DET, SAMPLING_PHILOX, SAMPLING_ARRAYS = 0, 1, 2
 
@@ -61,7 +62,8 @@ class Stages(C.Structure):
 
 class Timing(C.Structure):
     _fields_ = [("total_ms", C.c_float), ("mlp_coarse_ms", C.c_float), ("mlp_fine_ms", C.c_float),
-                ("sampling_ms", C.c_float), ("composite_ms", C.c_float), ("kernel_launches", C.c_int32)]
+                ("sampling_ms", C.c_float), ("composite_ms", C.c_float), ("kernel_launches", C.c_int32),
+                ("coarse_refine_ms", C.c_float), ("coarse_samples", C.c_int64), ("coarse_refined", C.c_int64)]
 
 
 class Tensor(C.Structure):

@@ -35,10 +35,18 @@ struct DevBuf {
   size_t cap = 0;
   int reserve(size_t bytes) {
     if (bytes <= cap) return NERF_OK;
-    if (p) cudaFree(p);
-    p = nullptr;
-    cap = 0;
-    NERF_CUDA(cudaMalloc(&p, bytes));
+    void* q = nullptr;
+    if (cudaMalloc(&q, bytes) != cudaSuccess) {
+      // not enough room for old + new: the contents are scratch, so give the old block back and try once more
+      cudaGetLastError();
+      if (p) cudaFree(p);
+      p = nullptr;
+      cap = 0;
+      NERF_CUDA(cudaMalloc(&q, bytes));
+    } else if (p) {
+      cudaFree(p);
+    }
+    p = q;
     cap = bytes;
     return NERF_OK;
   }
@@ -58,7 +66,7 @@ struct DeviceNet {
   TcWeights tcx3;         // fp16 hi / lo split tiles of the fp16x3 mode (mlp_tc_x3.cu)
 };
 
-enum StageKind { ST_SAMPLING = 0, ST_MLP_COARSE, ST_MLP_FINE, ST_COMPOSITE, ST_COUNT };
+enum StageKind { ST_SAMPLING = 0, ST_MLP_COARSE, ST_MLP_FINE, ST_COMPOSITE, ST_COARSE_REFINE, ST_COUNT };
 
 }  // namespace
 }  // namespace nerf
@@ -72,6 +80,13 @@ struct nerf_ctx {
   std::recursive_mutex mu;
   DeviceNet nets[2];
   DevBuf dirs, tc, sigc, wc, tf, sigf, rgbf, out, in_a, in_b, jit, uni;
+  // two-pass coarse densities of the mixed mode: ids of the samples the split-operand kernel re-evaluates
+  DevBuf sel_list, sel_count;
+  bool coarse_select = true;    // NERF_B200_COARSE_SELECT=0: split-operand kernel over every coarse sample
+  // NERF_B200_SELECT_MARGIN: bound on the fp16 pass's pre-activation error near zero.  Measured (scripts/select_check.py,
+  // 800x800 reference pose): the frame stays bit-identical down to 0.03, so 0.5 keeps a factor 16.
+  float select_margin = 0.5f;
+  float select_tau = 12.0f;     // NERF_B200_SELECT_TAU: optical depth behind which no coarse weight survives (T < 6e-6)
   // 8-bit output path: two device frames + two pinned host frames so that the copy of one view overlaps the next render
   DevBuf q8[2], depth, acc;
   uint8_t* pinned[2] = {nullptr, nullptr};
@@ -83,8 +98,12 @@ struct nerf_ctx {
   std::vector<Span> spans;
   size_t spans_used = 0;
   cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+  cudaEvent_t ev_busy = nullptr;  // end of the last enqueued call, on whichever stream it ran
+  bool busy_recorded = false;
   bool have_timing = false;
   int launches = 0;
+  int64_t refine_total = 0;     // coarse samples that went through the two-pass path since timing_start
+  bool refine_pending = false;  // sel_count holds the last chunk's list length
   int64_t chunk_rays = 1 << 20;
   struct VmmFrame { CUmemGenericAllocationHandle handle; size_t size; };
   std::map<void*, VmmFrame> vmm_frames;  // nerf_shared_frame_*_fd mappings owned by this context
@@ -182,9 +201,16 @@ int create_common(const TensorMap& coarse, const TensorMap& fine, int device, ne
     const long long v = std::atoll(e);
     if (v > 0) ctx->chunk_rays = v;
   }
+  if (const char* e = std::getenv("NERF_B200_COARSE_SELECT")) ctx->coarse_select = std::atoi(e) != 0;
+  if (const char* e = std::getenv("NERF_B200_SELECT_MARGIN")) ctx->select_margin = (float)std::atof(e);
+  if (const char* e = std::getenv("NERF_B200_SELECT_TAU")) ctx->select_tau = (float)std::atof(e);
   cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = init_mlp_tc();  // function attributes, once per device
+  if (e == cudaSuccess) e = init_mlp_tc_x3();
+  if (e == cudaSuccess) e = init_sampling();
   if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev_begin);
   if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev_end);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_busy, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking);
   for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
     e = cudaEventCreateWithFlags(&ctx->ev_q[i], cudaEventDisableTiming);
@@ -195,7 +221,9 @@ int create_common(const TensorMap& coarse, const TensorMap& fine, int device, ne
     delete ctx;
     return NERF_E_CUDA;
   }
-  rc = upload_network(coarse, &ctx->nets[0], cache ? cache->images[0] : nullptr);
+  rc = ctx->sel_count.reserve(256);
+  if (rc == NERF_OK && cudaMemset(ctx->sel_count.p, 0, 256) != cudaSuccess) rc = NERF_E_CUDA;
+  if (rc == NERF_OK) rc = upload_network(coarse, &ctx->nets[0], cache ? cache->images[0] : nullptr);
   if (rc == NERF_OK) rc = upload_network(fine, &ctx->nets[1], cache ? cache->images[1] : nullptr);
   if (rc != NERF_OK) {
     nerf_destroy(ctx);
@@ -249,8 +277,11 @@ int run_mlp(nerf_ctx* c, int net, const SampleSrc& src, const SampleDst& dst, in
     case NERF_PREC_BF16:
       e = launch_mlp_tc(c->nets[net].tc[0], src, dst, c->sm_count, s);
       break;
-    case NERF_PREC_FP16:
     case NERF_PREC_TF32:
+      set_error("NERF_PREC_TF32 is not a mode of this library (no kind::tf32 kernel): use NERF_PREC_FP16, the same "
+                "10-bit operand mantissa at twice the rate");
+      return NERF_E_UNSUPPORTED;
+    case NERF_PREC_FP16:
       e = launch_mlp_tc(c->nets[net].tc[1], src, dst, c->sm_count, s);
       break;
     case NERF_PREC_FP16X3:
@@ -330,11 +361,36 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
     src.dirs = c->dirs.as<float>();
     src.t = c->tc.as<float>();
     for (int i = 0; i < 3; ++i) src.origin[i] = cam.origin[i];
-    SampleDst dst{c->sigc.as<float>(), nullptr};  // coarse colour is discarded by the reference (lib.rs:404)
-    span_begin(c, ST_MLP_COARSE, s);
-    rc = run_mlp(c, NERF_NET_COARSE, src, dst, precision, s);
-    span_end(c, s);
-    if (rc) return rc;
+    SampleDst dst{c->sigc.as<float>(), nullptr, 0.0f};  // coarse colour is discarded by the reference (lib.rs:404)
+    if (precision == NERF_PREC_MIXED && c->coarse_select) {
+      // Two-pass coarse densities: fp16 pre-activations for every sample, then the split-operand kernel over the
+      // compacted list of samples whose density can reach a coarse weight (typically 8-10 % of them).
+      if ((rc = c->sel_list.reserve(n * nc * 4)) || (rc = c->sel_count.reserve(256))) return rc;
+      span_begin(c, ST_MLP_COARSE, s);
+      dst.sigma_floor = -INFINITY;
+      rc = run_mlp(c, NERF_NET_COARSE, src, dst, NERF_PREC_FP16, s);
+      span_end(c, s);
+      if (rc) return rc;
+      span_begin(c, ST_COARSE_REFINE, s);
+      NERF_CUDA(cudaMemsetAsync(c->sel_count.p, 0, 4, s));
+      NERF_CUDA(launch_coarse_select(c->sigc.as<float>(), c->tc.as<float>(), n, nc, cam.far_, c->select_margin,
+                                     c->select_tau, c->sel_list.as<int32_t>(), c->sel_count.as<uint32_t>(), s));
+      ++c->launches;
+      SampleSrc ref = src;
+      ref.index = c->sel_list.as<int32_t>();
+      ref.count = c->sel_count.as<uint32_t>();
+      dst.sigma_floor = 0.0f;
+      rc = run_mlp(c, NERF_NET_COARSE, ref, dst, NERF_PREC_FP16X3, s);
+      span_end(c, s);
+      if (rc) return rc;
+      c->refine_total += n * nc;
+      c->refine_pending = true;
+    } else {
+      span_begin(c, ST_MLP_COARSE, s);
+      rc = run_mlp(c, NERF_NET_COARSE, src, dst, precision, s);
+      span_end(c, s);
+      if (rc) return rc;
+    }
 
     span_begin(c, ST_SAMPLING, s);
     NERF_CUDA(launch_importance(c->tc.as<float>(), c->sigc.as<float>(), nullptr, nc, nf, cam.far_, mode, seed,
@@ -361,13 +417,25 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
   return NERF_OK;
 }
 
+// Every call that enqueues work on the context's workspaces goes through timing_start / timing_stop.  The workspaces
+// are one set per context, so a call on another stream must not start before the previous call's kernels have finished
+// with them: timing_stop records ev_busy on the call's stream, timing_start makes the next call's stream wait for it
+// (a no-op on the same stream).  Calls are serialised on the device, never on the host.
 void timing_start(nerf_ctx* c, cudaStream_t s) {
+  if (c->busy_recorded) cudaStreamWaitEvent(s, c->ev_busy, 0);
   c->spans_used = 0;
   c->launches = 0;
+  c->refine_total = 0;
+  c->refine_pending = false;
+  if (c->sel_count.p) cudaMemsetAsync(c->sel_count.p, 0, 8, s);  // [0] list length of the chunk, [1] running total
   c->have_timing = true;
   cudaEventRecord(c->ev_begin, s);
 }
-void timing_stop(nerf_ctx* c, cudaStream_t s) { cudaEventRecord(c->ev_end, s); }
+void timing_stop(nerf_ctx* c, cudaStream_t s) {
+  cudaEventRecord(c->ev_end, s);
+  cudaEventRecord(c->ev_busy, s);
+  c->busy_recorded = true;
+}
 
 }  // namespace
 }  // namespace nerf
@@ -546,7 +614,7 @@ void nerf_destroy(nerf_ctx* c) {
     DeviceGuard g(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     for (DevBuf* b : {&c->dirs, &c->tc, &c->sigc, &c->wc, &c->tf, &c->sigf, &c->rgbf, &c->out, &c->in_a, &c->in_b,
-                      &c->jit, &c->uni, &c->q8[0], &c->q8[1], &c->depth, &c->acc})
+                      &c->jit, &c->uni, &c->q8[0], &c->q8[1], &c->depth, &c->acc, &c->sel_list, &c->sel_count})
       b->release();
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
     for (int i = 0; i < 2; ++i) {
@@ -566,6 +634,7 @@ void nerf_destroy(nerf_ctx* c) {
     }
     if (c->ev_begin) cudaEventDestroy(c->ev_begin);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
+    if (c->ev_busy) cudaEventDestroy(c->ev_busy);
     if (c->stream) cudaStreamDestroy(c->stream);
   }
   delete c;
@@ -1145,9 +1214,19 @@ int nerf_get_timing(nerf_ctx* c, nerf_timing* out) {
       case ST_MLP_COARSE: out->mlp_coarse_ms += ms; break;
       case ST_MLP_FINE: out->mlp_fine_ms += ms; break;
       case ST_COMPOSITE: out->composite_ms += ms; break;
+      case ST_COARSE_REFINE:
+        out->mlp_coarse_ms += ms;
+        out->coarse_refine_ms += ms;
+        break;
     }
   }
   out->kernel_launches = c->launches;
+  out->coarse_samples = c->refine_total;
+  if (c->refine_pending) {  // ev_end has completed, so the counters are final
+    uint32_t cnt[2] = {0, 0};
+    NERF_CUDA(cudaMemcpy(cnt, c->sel_count.p, sizeof(cnt), cudaMemcpyDeviceToHost));
+    out->coarse_refined = cnt[1];
+  }
   return NERF_OK;
 }
 

@@ -36,6 +36,9 @@ struct NetF32 {
 // Where the samples of an MLP launch come from.
 //   mode 0: forward_batch — points [3][B] feature-major + dirs [B][3]          (network.rs:197)
 //   mode 1: render        — sample g belongs to ray g / S; p = origin + dir_hat * t   (lib.rs:396,436)
+//   mode 1 + index        — refinement pass over a compacted list: launch slot i evaluates sample g = index[i] and
+//                           stores its outputs at g; the number of slots is read from *count on the device
+//                           (the list is built by coarse_select_kernel in the same stream), B is ignored
 struct SampleSrc {
   int mode;
   int S;                // samples per ray (mode 1)
@@ -44,11 +47,16 @@ struct SampleSrc {
   const float* dirs;    // mode 0: [B][3]; mode 1: [n_rays][3]
   const float* t;       // mode 1: [n_rays][S]
   float origin[3];
+  const int32_t* index;   // mode 1 only, nullable: sample ids of the launch slots
+  const uint32_t* count;  // with index: device-resident number of slots
 };
 
 struct SampleDst {
   float* sigma;  // [B]
   float* rgb;    // [B][3] or nullptr: skip bottleneck/viewdirs/rgb (the reference discards coarse rgb, lib.rs:404)
+  // sigma = max(alpha(h8), sigma_floor): 0 is the reference's ReLU (network.rs:216, fmaxf also maps NaN to 0);
+  // -inf stores the pre-activation itself (first pass of the two-pass coarse densities)
+  float sigma_floor;
 };
 
 // Camera constants hoisted out of get_ray_dir (lib.rs:216-226): they do not depend on the pixel, so
@@ -87,6 +95,7 @@ __host__ __device__ inline float philox_uniform(uint64_t seed, uint32_t pixel, u
 // mlp_fp32.cu
 cudaError_t launch_mlp_fp32(const NetF32& net, const SampleSrc& src, const SampleDst& dst, cudaStream_t s);
 // sampling.cu
+cudaError_t init_sampling();
 cudaError_t launch_raygen_stratified(const RayBasis& rb, int nc, int mode, uint64_t seed, const float* d_jitter,
                                      int64_t ray_begin, int64_t n_rays, float* d_dirs, float* d_tc, cudaStream_t s);
 cudaError_t launch_ray_dirs(const RayBasis& rb, int64_t ray_begin, int64_t n_rays, float* d_dirs, cudaStream_t s);
@@ -95,6 +104,11 @@ cudaError_t launch_importance(const float* d_tc, const float* d_sigc, const floa
                               int mode,
                               uint64_t seed, const float* d_u, int64_t ray_begin, int64_t n_rays, float* d_tf,
                               float* d_wc_or_null, cudaStream_t s);
+// Two-pass coarse densities: d_sig holds the single-pass fp16 pre-activations on entry and
+// relu(pre-activation) on return; the ids of the samples whose density can reach the coarse weights are appended to
+// d_list, their number to *d_count (zeroed by the caller).
+cudaError_t launch_coarse_select(float* d_sig, const float* d_t, int64_t n_rays, int nc, float far_, float margin,
+                                 float tau_cut, int32_t* d_list, uint32_t* d_count, cudaStream_t s);
 cudaError_t launch_weights(const float* d_sigma, const float* d_t, int64_t n_rays, int n, float far_, float* d_w,
                            cudaStream_t s);
 cudaError_t launch_quantize(const float* d_rgb, int64_t n_pixels, int channels, uint8_t* d_out, cudaStream_t s);

@@ -193,7 +193,10 @@ __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t threads) {
 
 
 // ------------------------------------------------------------------------------------------ the kernel
-template <bool kFp16>
+// kRawSigma: store the density head's pre-activation alpha(h8) instead of relu(alpha(h8)) (first pass of the two-pass
+// coarse densities).  A template parameter, not a run-time flag: reading one more kernel parameter in the epilogue
+// made ptxas spill two registers of the 112-register epilogue warps.
+template <bool kFp16, bool kRawSigma>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ chunks, const SampleSrc src,
               const SampleDst dst, unsigned long long* __restrict__ trace) {
@@ -491,7 +494,7 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
           float v = sig[s];
 #pragma unroll
           for (uint32_t k = 1; k < 4; ++k) v += reinterpret_cast<const float*>(aux + sw128_offset(row, 32u + 8u * k))[3];
-          if (valid[s]) dst.sigma[g[s]] = fmaxf(v, 0.0f);
+          if (valid[s]) dst.sigma[g[s]] = kRawSigma ? v : fmaxf(v, 0.0f);
         }
       }
       if (want_rgb) {
@@ -672,6 +675,14 @@ void free_tc_weights(TcWeights* w) {
   w->bytes = 0;
 }
 
+cudaError_t init_mlp_tc() {  // once per process and device, at context creation
+  cudaError_t e = cudaFuncSetAttribute(mlp_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(mlp_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(mlp_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+}
+
 cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
                           cudaStream_t s) {
   if (src.B == 0) return cudaSuccess;
@@ -685,17 +696,16 @@ cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const Sample
   const size_t trace_bytes = 7 * 2 * kTraceCap * sizeof(unsigned long long);
   if (trace_path != nullptr) {
     if ((e = cudaMalloc(&trace, trace_bytes)) != cudaSuccess) return e;
-    cudaMemsetAsync(trace, 0, trace_bytes, s);
+    if ((e = cudaMemsetAsync(trace, 0, trace_bytes, s)) != cudaSuccess) {
+      cudaFree(trace);
+      return e;
+    }
   }
-  if (w.fmt == 1) {
-    e = cudaFuncSetAttribute(mlp_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-    if (e != cudaSuccess) return e;
-    mlp_tc_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace);
-  } else {
-    e = cudaFuncSetAttribute(mlp_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-    if (e != cudaSuccess) return e;
-    mlp_tc_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace);
-  }
+  const bool raw = dst.sigma_floor < 0.0f;
+  if (raw && (w.fmt != 1 || dst.rgb != nullptr)) return cudaErrorInvalidValue;  // only the fp16 density-only pass has it
+  if (raw) mlp_tc_kernel<true, true><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace);
+  else if (w.fmt == 1) mlp_tc_kernel<true, false><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace);
+  else mlp_tc_kernel<false, false><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace);
   e = cudaGetLastError();
   if (trace != nullptr) {
     std::vector<unsigned long long> h(trace_bytes / 8);

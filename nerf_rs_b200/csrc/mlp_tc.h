@@ -38,6 +38,9 @@ size_t tc_image_bytes(int fmt);  // length of that stream: the kernels' bulk cop
 int upload_tc_weights(const uint8_t* img, size_t bytes, int fmt, const TensorMap& t, TcWeights* out);
 int build_tc_weights(const TensorMap& t, int fmt, TcWeights* out);
 void free_tc_weights(TcWeights* w);
+// Opt the kernels into their dynamic shared memory size (once per device, at context creation).
+cudaError_t init_mlp_tc();
+cudaError_t init_mlp_tc_x3();
 cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
                           cudaStream_t s);
 cudaError_t launch_mlp_tc_x3(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,

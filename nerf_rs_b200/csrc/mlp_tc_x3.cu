@@ -168,6 +168,9 @@ __device__ __forceinline__ void write_pe16(uint8_t* aux_row_hi, uint32_t r8, con
 }
 
 // ------------------------------------------------------------------------------------------ the kernel
+// kGather: refinement launch over a compacted sample list (SampleSrc::index / count), a separate instantiation so that
+// the plain kernel keeps its register allocation (no spills at the 112-register epilogue cap).
+template <bool kGather>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 mlp_tc_x3_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ chunks, const SampleSrc src,
                  const SampleDst dst) {
@@ -185,7 +188,9 @@ mlp_tc_x3_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__
   const int64_t pair_id = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const bool want_rgb = dst.rgb != nullptr;
   const int n_layers = want_rgb ? kNumLayers : 8;
-  const int64_t n_tiles = (src.B + kTileM - 1) / kTileM;
+  // refinement launches (SampleSrc::index) learn their size from the list the selection kernel has just built
+  const int64_t B = kGather ? (int64_t)__ldg(src.count) : src.B;
+  const int64_t n_tiles = (B + kTileM - 1) / kTileM;
   const int64_t n_units = (n_tiles + 1) / 2;  // unit u = tiles 2u (leader CTA) and 2u + 1 (peer CTA)
 
   if (threadIdx.x == 0) {
@@ -339,22 +344,36 @@ mlp_tc_x3_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__
     };
 
     float4 pre;  // {p.xyz, -} for explicit points, {dir.xyz, t} for samples along rays
+    int32_t g_pre = 0;  // kGather: the sample id `pre` belongs to (the launch slot otherwise, recomputed where needed)
+    int32_t idx_pre = 0;  // index-list entry of this row's slot in the unit the NEXT prefetch fetches: loaded one unit
+                          // earlier, so that the dependent loads of dirs / t never wait for it inside a drain
+    auto load_index = [&](int64_t unit) {
+      const int64_t gi = (2 * unit + (int64_t)rank) * kTileM + row;
+      if (kGather && gi < B) idx_pre = __ldg(src.index + gi);
+    };
     auto prefetch = [&](int64_t unit) {
       const int64_t gi = (2 * unit + (int64_t)rank) * kTileM + row;
       pre = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (gi < src.B) {
+      if (gi < B) {
         if (src.mode == 0) {
-          pre = make_float4(src.points[gi], src.points[src.B + gi], src.points[2 * src.B + gi], 0.f);
+          pre = make_float4(src.points[gi], src.points[B + gi], src.points[2 * B + gi], 0.f);
+        } else if (kGather) {
+          g_pre = idx_pre;
+          const int32_t ray = g_pre / src.S;
+          pre = make_float4(src.dirs[ray * 3 + 0], src.dirs[ray * 3 + 1], src.dirs[ray * 3 + 2], src.t[g_pre]);
         } else {
           const int64_t ray = gi / src.S;
           pre = make_float4(src.dirs[ray * 3 + 0], src.dirs[ray * 3 + 1], src.dirs[ray * 3 + 2], src.t[gi]);
         }
       }
+      if (kGather) load_index(unit + n_pairs);
     };
+    if (kGather) load_index(pair_id);
     prefetch(pair_id);
     for (int64_t unit = pair_id; unit < n_units; unit += n_pairs) {
-      const int64_t g = (2 * unit + (int64_t)rank) * kTileM + row;
-      const bool valid = g < src.B;  // tiles past the end run the same barrier protocol on zeros
+      const int64_t slot = (2 * unit + (int64_t)rank) * kTileM + row;
+      const int64_t g = kGather ? (int64_t)g_pre : slot;
+      const bool valid = slot < B;  // tiles past the end run the same barrier protocol on zeros
       float p[3] = {pre.x, pre.y, pre.z};
       float dir[3] = {0.f, 0.f, 0.f};
       if (src.mode == 0) {
@@ -508,15 +527,24 @@ void build_tc_x3_image(const TensorMap& t, std::vector<uint8_t>* out) {
 
 cudaError_t launch_mlp_tc_x3(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
                              cudaStream_t s) {
-  if (src.B == 0) return cudaSuccess;
+  if (src.B == 0) return cudaSuccess;  // with a device-resident count, B is the upper bound of it
   const int64_t n_tiles = (src.B + kTileM - 1) / kTileM;
   const int64_t n_units = (n_tiles + 1) / 2;  // a CTA pair works on two tiles at a time
   const int64_t max_pairs = sm_count / 2;
   const int grid = 2 * (int)(n_units < max_pairs ? n_units : max_pairs);
-  cudaError_t e = cudaFuncSetAttribute(mlp_tc_x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-  if (e != cudaSuccess) return e;
-  mlp_tc_x3_kernel<<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst);
+  if (src.index != nullptr) {
+    if (src.mode != 1 || src.count == nullptr) return cudaErrorInvalidValue;
+    mlp_tc_x3_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst);
+  } else {
+    mlp_tc_x3_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst);
+  }
   return cudaGetLastError();
+}
+
+cudaError_t init_mlp_tc_x3() {  // once per process and device, at context creation
+  cudaError_t e = cudaFuncSetAttribute(mlp_tc_x3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(mlp_tc_x3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
 }
 
 }  // namespace nerf

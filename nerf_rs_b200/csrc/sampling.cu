@@ -276,6 +276,100 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) importance_kernel(
   }
 }
 
+// Two-pass coarse densities, selection step.  `sig` arrives as the single-pass fp16 kernel's density
+// PRE-activations alpha(h8) and leaves as relu of them; the samples whose density the split-operand kernel has to
+// re-evaluate are appended to `list`.  A sample is skipped only if its exact density provably cannot reach a coarse
+// weight (compute_weights, lib.rs:250-283):
+//   - pre <= -margin: the exact pre-activation is negative too (margin bounds the single-pass error), sigma = 0 both ways;
+//   - optical depth in front of it >= tau_cut: transmittance there is far below the 1e-4 at which the reference zeroes
+//     every later weight (lib.rs:276-279), whatever this sample's density is.  The optical depth is accumulated from the
+//     fp16 densities; tau_cut leaves e^-(tau_cut - 9.21) of slack for their error, and every sample in front of the
+//     cut is itself re-evaluated or exactly zero.
+// One warp per ray, one list reservation (atomicAdd) per CTA of 8 rays.
+__global__ void __launch_bounds__(kWarpsPerCta * 32) coarse_select_kernel(float* __restrict__ sig,
+                                                                          const float* __restrict__ t, int64_t n_rays,
+                                                                          int nc, float far_, float margin,
+                                                                          float tau_cut, int32_t* __restrict__ list,
+                                                                          uint32_t* __restrict__ count) {
+  __shared__ uint32_t s_cnt[kWarpsPerCta], s_base;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int64_t ray0 = blockIdx.x * (int64_t)kWarpsPerCta; ray0 < n_rays; ray0 += (int64_t)gridDim.x * kWarpsPerCta) {
+    const int64_t ray = ray0 + warp;
+    const bool live = ray < n_rays;
+    // pass 1: flags (kept as ballots in registers for up to 8 rounds = 256 samples, recomputed otherwise)
+    uint32_t total = 0;
+    float carry = 0.0f;
+    if (live) {
+      for (int base = 0; base < nc; base += 32) {
+        const int i = base + lane;
+        float pre = -1e30f, od = 0.0f;
+        if (i < nc) {
+          pre = sig[ray * nc + i];
+          const float ti = t[ray * nc + i];
+          float delta = (i + 1 < nc) ? (t[ray * nc + i + 1] - ti) : (far_ - ti);
+          if (delta < 0.0f) delta = 0.0f;
+          od = fmaxf(pre, 0.0f) * delta;
+        }
+        float incl = od;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const float q = __shfl_up_sync(kFull, incl, d);
+          if (lane >= d) incl += q;
+        }
+        const float before = carry + (incl - od);
+        carry += __shfl_sync(kFull, incl, 31);
+        // NaN pre-activations (broken weights) are selected: both comparisons are written to be true for NaN
+        const bool flag = i < nc && !(pre <= -margin) && !(before >= tau_cut);
+        total += __popc(__ballot_sync(kFull, flag));
+      }
+    }
+    if (lane == 0) s_cnt[warp] = total;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t sum = 0;
+      for (int w = 0; w < kWarpsPerCta; ++w) {
+        const uint32_t c = s_cnt[w];
+        s_cnt[w] = sum;
+        sum += c;
+      }
+      s_base = sum ? atomicAdd(count, sum) : 0u;
+      if (sum) atomicAdd(count + 1, sum);  // running total over the chunks of a render (nerf_timing::coarse_refined)
+    }
+    __syncthreads();
+    // pass 2: same flags again (the loads hit L1), write the ids and the clamped densities
+    if (live) {
+      uint32_t pos = s_base + s_cnt[warp];
+      carry = 0.0f;
+      for (int base = 0; base < nc; base += 32) {
+        const int i = base + lane;
+        float pre = -1e30f, od = 0.0f;
+        if (i < nc) {
+          pre = sig[ray * nc + i];
+          const float ti = t[ray * nc + i];
+          float delta = (i + 1 < nc) ? (t[ray * nc + i + 1] - ti) : (far_ - ti);
+          if (delta < 0.0f) delta = 0.0f;
+          od = fmaxf(pre, 0.0f) * delta;
+        }
+        float incl = od;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const float q = __shfl_up_sync(kFull, incl, d);
+          if (lane >= d) incl += q;
+        }
+        const float before = carry + (incl - od);
+        carry += __shfl_sync(kFull, incl, 31);
+        const bool flag = i < nc && !(pre <= -margin) && !(before >= tau_cut);
+        const uint32_t mask = __ballot_sync(kFull, flag);
+        if (flag) list[pos + __popc(mask & ((1u << lane) - 1u))] = (int32_t)(ray * nc + i);
+        pos += __popc(mask);
+        __syncwarp();  // every lane has read its neighbours' pre-activations (t only) before anyone overwrites sig
+        if (i < nc) sig[ray * nc + i] = fmaxf(pre, 0.0f);
+      }
+    }
+    __syncthreads();  // s_cnt / s_base are reused by the next group of rays
+  }
+}
+
 // compute_weights alone (stage parity entry point).
 __global__ void __launch_bounds__(kWarpsPerCta * 32) weights_kernel(const float* __restrict__ sigma,
                                                                     const float* __restrict__ t, int64_t n_rays,
@@ -337,6 +431,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) composite_kernel(const floa
   }
 }
 
+constexpr size_t kImportanceMaxSmem = 200 * 1024;  // check_render_args (api.cu) refuses sample counts beyond it
 size_t importance_smem_bytes(int nc, int nf) {
   return (size_t)kWarpsPerCta * (5 * (size_t)nc + next_pow2(nf > 0 ? nf : 1) + next_pow2(nc)) * sizeof(float);
 }
@@ -350,6 +445,10 @@ inline int grid_for(int64_t work_items, int per_cta) {
 }
 
 }  // namespace
+
+cudaError_t init_sampling() {  // once per device, at context creation
+  return cudaFuncSetAttribute(importance_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kImportanceMaxSmem);
+}
 
 cudaError_t launch_raygen_stratified(const RayBasis& rb, int nc, int mode, uint64_t seed, const float* d_jitter,
                                      int64_t ray_begin, int64_t n_rays, float* d_dirs, float* d_tc, cudaStream_t s) {
@@ -370,11 +469,17 @@ cudaError_t launch_importance(const float* d_tc, const float* d_sigc, const floa
                               float* d_wc, cudaStream_t s) {
   if (n_rays == 0) return cudaSuccess;
   const size_t smem = importance_smem_bytes(nc, nf);
-  if (smem > 200 * 1024) return cudaErrorInvalidValue;
-  cudaError_t e = cudaFuncSetAttribute(importance_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return e;
+  if (smem > kImportanceMaxSmem) return cudaErrorInvalidValue;
   importance_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, smem, s>>>(
       d_tc, d_sigc, d_w_in, nc, nf, far_, mode, seed, d_u, ray_begin, n_rays, d_tf, d_wc);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_coarse_select(float* d_sig, const float* d_t, int64_t n_rays, int nc, float far_, float margin,
+                                 float tau_cut, int32_t* d_list, uint32_t* d_count, cudaStream_t s) {
+  if (n_rays == 0) return cudaSuccess;
+  coarse_select_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, 0, s>>>(d_sig, d_t, n_rays, nc, far_,
+                                                                                    margin, tau_cut, d_list, d_count);
   return cudaGetLastError();
 }
 

@@ -24,10 +24,12 @@ class Network:
         self._r = renderer
         self.net_id = net_id
 
-    def forward_batch(self, points, view_dirs, precision="mixed"):
+    def forward_batch(self, points, view_dirs, precision="fp16x3"):
         """points: [3, B] feature-major (the reference's Matrix 3xB); view_dirs: [B, 3].
 
-        Returns (rgb [B, 3], sigma [B]).  An empty batch returns empty arrays (network.rs:199-201)."""
+        Returns (rgb [B, 3], sigma [B]).  An empty batch returns empty arrays (network.rs:199-201).  The default
+        precision is fp16x3: the one tensor-core mode that passes the reference's own unit test (1e-2 abs on sigma up
+        to 213, src/lib.rs:732-742) with margin; render_image defaults to "mixed", where the image bound applies."""
         points = _f32(points)
         view_dirs = _f32(view_dirs)
         B = points.shape[1] if points.ndim == 2 else 0
@@ -41,7 +43,7 @@ class Network:
                                         _p(rgb), _p(sigma)))
         return rgb, sigma
 
-    def forward_batch_device(self, d_points, d_dirs, B, d_rgb, d_sigma, precision="mixed", stream=0):
+    def forward_batch_device(self, d_points, d_dirs, B, d_rgb, d_sigma, precision="fp16x3", stream=0):
         """Same on device pointers (ints), enqueued on `stream` without synchronising."""
         _check(lib().nerf_forward_batch_device(self._r._h, self.net_id, d_points, d_dirs, B, _prec(precision), d_rgb,
                                                d_sigma, stream))

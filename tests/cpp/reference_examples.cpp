@@ -7,7 +7,7 @@
 // original hard-codes the expected numbers as literals (lib.rs:759-847); this reads the same numbers from
 // lego_rust/tf_reference_samples.json, where the reference keeps them in f64-printed form.
 //
-//   usage: reference_examples <lego_rust dir> [precision: fp32 | fp16x3 | fp16 | bf16 | mixed] [out.ppm]
+//   usage: reference_examples <lego_rust dir> [precision: default | fp32 | fp16x3 | fp16 | bf16 | mixed] [out.ppm]
 // With a third argument it also goes through the render half of the API the way render_cli_image does (lib.rs:647-677):
 // camera_from_samples at 32 x 24 with 64 coarse samples, render_image with 128 fine samples (deterministic sampling
 // so that the caller can compare bytes), save_ppm.
@@ -61,6 +61,26 @@ void assert_close(float got, double want, const char* what, int example, int sam
   }
 }
 
+// The tensors of <dir> the way load_network_from_dir reads them (lib.rs:35-42,63-74,108-174), but kept by the caller:
+// little-endian f32 files, kernels [in x out] row-major.  Feeds Network::create, the mirror of Network::new.
+nerf_rs::Network network_from_layers(const std::string& dir, int precision) {
+  auto layer = [&](const std::string& stem, int32_t in, int32_t out) {
+    auto read = [&](const std::string& name, size_t count) {
+      std::ifstream f(dir + "/" + name + ".bin", std::ios::binary);
+      std::vector<float> v(count);
+      if (!f.read(reinterpret_cast<char*>(v.data()), (std::streamsize)(count * 4))) throw nerf_rs::Panic("read " + name);
+      return v;
+    };
+    return nerf_rs::Layer(nerf_rs::Matrix(in, out, read(stem + "_kernel", (size_t)in * out)), read(stem + "_bias", out));
+  };
+  std::vector<nerf_rs::Layer> trunk;
+  for (int i = 0; i < 8; ++i) trunk.push_back(layer("dense" + std::to_string(i), i == 0 ? 63 : (i == 5 ? 319 : 256), 256));
+  nerf_rs::Network n = nerf_rs::Network::create(std::move(trunk), layer("bottleneck", 256, 256), layer("viewdirs", 283, 128),
+                                                layer("rgb", 128, 3), layer("alpha", 256, 1));
+  if (precision >= 0) n.set_precision(precision);
+  return n;
+}
+
 int precision_from(const char* s) {
   if (!std::strcmp(s, "fp32")) return NERF_PREC_FP32;
   if (!std::strcmp(s, "bf16")) return NERF_PREC_BF16;
@@ -76,11 +96,14 @@ int main(int argc, char** argv) {
   using namespace nerf_rs;
   try {
     const std::string root = argc > 1 ? argv[1] : "lego_rust";
-    const int precision = precision_from(argc > 2 ? argv[2] : "fp16x3");
+    const char* prec_name = argc > 2 ? argv[2] : "default";
     Network coarse = load_network_from_dir(root + "/coarse");  // lib.rs:756
     Network fine = load_network_from_dir(root + "/fine");      // lib.rs:757
-    coarse.set_precision(precision);
-    fine.set_precision(precision);
+    if (std::strcmp(prec_name, "default") != 0) {  // "default": exactly what a caller of the crate's API gets
+      const int precision = precision_from(prec_name);
+      coarse.set_precision(precision);
+      fine.set_precision(precision);
+    }
 
     std::ifstream f(root + "/tf_reference_samples.json");
     if (!f) throw Panic("read " + root + "/tf_reference_samples.json");
@@ -142,6 +165,32 @@ int main(int argc, char** argv) {
       }
       if (!panicked) {
         std::printf("FAIL width not a multiple of 8 must panic\n");
+        ++failures;
+      }
+      // Layer::new / Network::new (network.rs:75,181-195): the same networks from caller-held layers evaluate and
+      // render bit-identically to the ones load_network_from_dir built
+      const int p = std::strcmp(prec_name, "default") != 0 ? precision_from(prec_name) : -1;
+      const Network coarse2 = network_from_layers(root + "/coarse", p), fine2 = network_from_layers(root + "/fine", p);
+      Matrix pts = Matrix::zeros(3, 7);
+      std::vector<Vec3> dirs;
+      for (int32_t s = 0; s < 7; ++s) {
+        pts.set(0, s, 0.1f * (float)s - 0.3f);
+        pts.set(1, s, 0.05f * (float)s);
+        pts.set(2, s, 0.2f - 0.07f * (float)s);
+        dirs.push_back(Vec3(0.6f, 0.0f, -0.8f));
+      }
+      const struct { const Network *a, *b; } same[2] = {{&coarse, &coarse2}, {&fine, &fine2}};
+      for (const auto& n : same) {
+        const auto x = n.a->forward_batch(pts, dirs), y = n.b->forward_batch(pts, dirs);
+        if (std::memcmp(x.first.data(), y.first.data(), 7 * sizeof(Vec3)) != 0 ||
+            std::memcmp(x.second.data(), y.second.data(), 7 * sizeof(float)) != 0) {
+          std::printf("FAIL Network::new differs from load_network_from_dir in forward_batch\n");
+          ++failures;
+        }
+      }
+      const std::vector<Vec3> pixels2 = render_image(coarse2, fine2, camera, default_sample_counts().second, &det);
+      if (std::memcmp(pixels.data(), pixels2.data(), pixels.size() * sizeof(Vec3)) != 0) {
+        std::printf("FAIL Network::new pair renders a different image\n");
         ++failures;
       }
     }
