@@ -37,14 +37,18 @@ WORKLOAD = "lego 800x800, 64 coarse + 128 fine samples/ray, deterministic sampli
 
 
 PRECISION_NOTE = {
-    "mixed": "mixed: coarse network fp16x3 (split-fp16 operands, 3 tensor-core MMAs per product, f32-class densities that "
-             "place the fine samples), fine network fp16; f32 accumulate, heads / sampling / compositing f32. "
-             "800x800 frame vs the order-faithful f32 kernel: max 1.26/255, 0 pixels above 2/255, PSNR 90 dB",
-    "fp16": "fp16: both networks single-pass fp16 operands, f32 accumulate. 800x800 frame vs the f32 kernel: PSNR 71 dB, "
-            "99 of 640 000 pixels (thin structures) above 2/255",
-    "fp16x3": "fp16x3: both networks split-fp16 operands, 3 tensor-core MMAs per product; max 1.25/255, PSNR 106 dB",
+    "mixed": "mixed: coarse densities at fp16x3 accuracy (fp16 pass over every coarse sample, then split-fp16 operands - 3 "
+             "tensor-core MMAs per product - over the ~8 % of samples whose density can reach a coarse weight; bit-identical "
+             "to fp16x3 over every coarse sample), fine network fp16; f32 accumulate, heads / sampling / compositing f32. "
+             "See `parity` for the frame against the CPU oracle",
+    "fp16": "fp16: both networks single-pass fp16 operands, f32 accumulate; PSNR ~71 dB, ~100 of 640 000 pixels (thin "
+            "structures) above 2/255",
+    "fp16x3": "fp16x3: both networks split-fp16 operands, 3 tensor-core MMAs per product",
 }
-NCU_FINE_DRAM_GB = 0.520 + 1.914  # dram__bytes_read.sum + dram__bytes_write.sum, fine pass, 800x800 c64+f128
+# dram__bytes_read.sum + dram__bytes_write.sum of the fine-pass launch, 800x800 c64+f128: a CONSTANT copied from one
+# `ncu --set full` capture (file below), not measured by this run
+NCU_FINE_DRAM_GB = 0.520 + 1.914
+NCU_FINE_DRAM_SOURCE = "profiles/r01_mlp_tc_v15_ncu_full_summary.csv"
 
 
 def load_peaks():
@@ -62,7 +66,9 @@ def cpu_sample(threads=0, budget_s=15.0):
     import nerf_rs_b200 as nb
     cam = O.camera_from_json(os.path.join(nb.DATA_ROOT, "tf_reference_samples.json"))
     oc, of = O.Network(nb.DATA_ROOT + "/coarse"), O.Network(nb.DATA_ROOT + "/fine")
-    cores = O.num_threads() if threads <= 0 else threads
+    # torchrun exports OMP_NUM_THREADS=1 to every rank: ask the scheduler how many cores this process may use instead of
+    # taking OpenMP's default, so that the CPU arm is the same at every N
+    cores = len(os.sched_getaffinity(0)) if threads <= 0 else threads
     begin = (H // 2) * W
     n0 = 8 * cores  # calibration: one 8-ray strip per thread
     t0 = time.perf_counter()
@@ -199,7 +205,23 @@ def gpu_arm(args):
         frame = torch.empty((n_rays, 3), dtype=torch.float32, device=dev)  # rank 0 assembles the frame here
         mine = frame[rb:re_] if world == 1 else torch.empty((n_local, 3), dtype=torch.float32, device=dev)
         mine_ptr = mine.data_ptr()
-    pinned = torch.empty((n_rays, 3), dtype=torch.float32).pin_memory()
+    # The e2e leg goes through the public host API (nerf_render) on EVERY rank: rank k renders its ray range straight into
+    # its rows of one host frame.  With N > 1 that frame is a POSIX shared-memory file mapped by every rank and
+    # page-locked (cudaHostRegister) in each, so the device-to-host copies are pinned copies as at N = 1.
+    shm_path = None
+    if world == 1:
+        pinned = torch.empty((n_rays, 3), dtype=torch.float32).pin_memory()
+        host_frame = pinned.numpy()
+    else:
+        shm_path = f"/dev/shm/nerf_b200_bench_{os.environ.get('MASTER_PORT', '0')}"
+        if rank == 0:
+            with open(shm_path, "wb") as f:
+                f.truncate(n_rays * 12)
+        dist.barrier()
+        host_frame = np.memmap(shm_path, dtype=np.float32, mode="r+", shape=(n_rays, 3))
+        err = torch.cuda.cudart().cudaHostRegister(host_frame.ctypes.data, n_rays * 12, 0)
+        if int(err) != 0:
+            print(f"rank {rank}: cudaHostRegister failed ({err}); the e2e copies run from pageable memory", file=sys.stderr)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream()
 
@@ -213,24 +235,20 @@ def gpu_arm(args):
         gather()
 
     def step_e2e():
-        if world == 1:
-            r.render_image(cam, W, H, NC, NF, precision=args.precision, out=pinned.numpy())  # host API, syncs
-        else:
-            step_device()
-            if use_peer:
-                sf.complete(stream)  # every rank's stores have landed in rank 0's HBM
-            if rank == 0:
-                pinned.copy_(frame, non_blocking=True)
-            stream.synchronize()
+        # nerf_render with host pointers: kernels + the D2H copy of this rank's rows, synchronous
+        r.render_image(cam, W, H, NC, NF, precision=args.precision, ray_begin=rb, ray_end=re_, out=host_frame[rb:re_])
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    extra = {"refine_ms": 0.0, "refined_frac": 0.0, "launches": 0}
+
     def timed(fn, k, use_events):
         """K steps, L2 flushed (untimed) before each one; returns summed step time in ms (max over ranks)."""
         tot = 0.0
+        extra["refine_ms"] = 0.0
         mlp_c = mlp_f = smp = comp = 0.0
         for _ in range(k):
             flush.zero_()
@@ -244,6 +262,9 @@ def gpu_arm(args):
                 ms = e0.elapsed_time(e1)
                 tm = r.timing()  # CUDA events recorded by the library on the same stream around each kernel
                 mlp_c += tm["mlp_coarse_ms"]; mlp_f += tm["mlp_fine_ms"]; smp += tm["sampling_ms"]; comp += tm["composite_ms"]
+                extra["refine_ms"] += tm["coarse_refine_ms"] / k
+                extra["refined_frac"] = tm["coarse_refined"] / max(tm["coarse_samples"], 1)
+                extra["launches"] = tm["kernel_launches"]
             else:
                 t0 = time.perf_counter()
                 fn()
@@ -261,6 +282,7 @@ def gpu_arm(args):
     clocks = ClockSampler(local) if rank == 0 else None
     total_ms, (mc, mf, sm_ms, cp_ms) = timed(step_device, args.steps, True)
     clk = clocks.stop() if clocks else {}
+    head = dict(extra)  # the headline loop's refinement share and launch count (later legs overwrite `extra`)
     stages_all = [[mc, mf, sm_ms, cp_ms]]
     if world > 1:  # every rank's mean stage times, for the record (which rank bounds the frame, and in which kernel)
         stages_all = [None] * world
@@ -272,6 +294,34 @@ def gpu_arm(args):
         fast_ms /= min(args.steps, 5)
     step_e2e()
     e2e_ms, _ = timed(step_e2e, args.steps, False)
+    # ---- parity, at every N: the frame the ranks assembled (through the device path and through the host API) against
+    # the frame rank 0 renders alone, bit for bit, and against the CPU oracle's whole frame (tests/golden/frame_800.npz)
+    step_device()
+    if use_peer:
+        sf.complete(stream)
+    barrier()
+    parity = None
+    if rank == 0:
+        dev_frame = frame.cpu().numpy()
+        host_copy = np.array(host_frame)  # what the e2e leg's last step left in host memory
+        solo = r.render_image(cam, W, H, NC, NF, precision=args.precision) if world > 1 else dev_frame
+        parity = {"bit_identical_to_1gpu": bool(np.array_equal(dev_frame, solo) and np.array_equal(host_copy, solo)),
+                  "assembled_by": "device path (" + ("peer stores" if use_peer else "nccl gather" if world > 1 else "one rank") +
+                                  ") and host API (nerf_render per rank into one shared pinned frame), both compared"}
+        gpath = os.path.join(ROOT, "tests", "golden", "frame_800.npz")
+        if os.path.exists(gpath):
+            z = np.load(gpath)
+            white = np.unpackbits(z["white"])[:n_rays].astype(bool)
+            want = np.ones((n_rays, 3), np.float32)
+            want[~white] = z["rgb"]
+            d = np.abs(host_copy - want).max(axis=1)
+            parity.update({
+                "vs": "CPU oracle (the reference's algorithm restated), whole 800x800 frame, identical deterministic sample "
+                      "positions (tests/golden/frame_800.npz)",
+                "pixels": int(d.size), "max_abs_diff_x255": float(d.max() * 255.0),
+                "pixels_over_2_255": int((d > 2.0 / 255.0).sum()), "pixels_over_1_255": int((d > 1.0 / 255.0).sum()),
+                "psnr_db": float(10.0 * np.log10(1.0 / max(float(np.mean((host_copy.astype(np.float64) - want) ** 2)), 1e-20)))})
+    barrier()
     rgb8_ms = many_ms = None
     if world == 1:
         # the same frame returned as 8-bit PPM bytes (3 B/ray over PCIe instead of 12), and a
@@ -292,24 +342,39 @@ def gpu_arm(args):
         value = n_rays / (ms * 1e-3)
         e2e_val = n_rays / (e2e_ms / args.steps * 1e-3)
         sustained, burst, hbm, kind = load_peaks()
-        fine_flop = n_local * (NC + NF) * FLOP_FINE  # rank 0's fine-pass launch (the dominant kernel)
+        fine_flop = n_local * (NC + NF) * FLOP_FINE  # rank 0's fine-pass launch
         ach = fine_flop / (mf * 1e-3) / 1e12
+        frame_tflops = n_rays * (NC * FLOP_COARSE + (NC + NF) * FLOP_FINE) / (ms * 1e-3) / 1e12
+        fine_kernel = {"fp16x3": "mlp_tc_x3_kernel (fine pass; 3 MMAs per product, credited once)",
+                       "fp32": "mlp_fp32_kernel (fine pass; CUDA cores)"}.get(args.precision, "mlp_tc_kernel (fine pass)")
+        coarse_kernel = {"fp16x3": "mlp_tc_x3_kernel (coarse pass, sigma only; 3 MMAs per product, credited once)",
+                         "fp32": "mlp_fp32_kernel (coarse pass)",
+                         "mixed": "mlp_tc_kernel fp16 over every coarse sample + coarse_select_kernel + mlp_tc_x3_kernel over "
+                                  "the selected samples (coarse pass, sigma only)"}.get(args.precision, "mlp_tc_kernel (coarse pass)")
+        c_ach = n_local * NC * FLOP_COARSE / (mc * 1e-3) / 1e12
+        dominant_is_fine = mf >= mc
         line = {
             "metric": "rays/s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "fp16" if args.precision == "mixed" else args.precision, "data": "synthetic",
             "config": {"workload": WORKLOAD, "precision": PRECISION_NOTE.get(args.precision, args.precision), "parallelism": f"ray-range x{world}",
                        "l2": "flushed (256 MiB memset, untimed) before every step; per-frame intermediates ~3 GB >> 126 MB L2",
+                       "timing": "value: per-rank CUDA events on the launching stream around the step (render + gather), every "
+                                 "step started from a barrier, max over ranks; e2e: host wall clock from the same barrier to the "
+                                 "return of nerf_render on each rank, max over ranks",
                        "gather": ("none" if world == 1 else
                                   "peer stores: every rank's compositing kernel writes its rows into rank 0's frame buffer over "
                                   "NVLink (the buffer is shared per allocation through the CUDA virtual-memory API), inside the timed region; "
                                   "no collective on the data path" if use_peer else
                                   "NCCL point-to-point group: every rank sends its rgb range to rank 0, inside the timed region")},
             "samples_per_s": value * (NC + NC + NF),
-            "tflops_frame": n_rays * (NC * FLOP_COARSE + (NC + NF) * FLOP_FINE) / (ms * 1e-3) / 1e12 ,
-            "stage_ms_rank0": {"mlp_coarse": mc, "mlp_fine": mf, "sampling": sm_ms, "composite": cp_ms},
+            "tflops_frame": frame_tflops,
+            "stage_ms_rank0": {"mlp_coarse": mc, "mlp_fine": mf, "sampling": sm_ms, "composite": cp_ms,
+                               "mlp_coarse_refine_part": head["refine_ms"]},
+            "coarse_refined_fraction": head["refined_frac"],
             "stage_ms_by_rank": [[round(x, 3) for x in st] for st in stages_all],  # [coarse, fine, sampling, composite]
-            "gpu_launches": 5 * args.steps,
+            "gpu_launches": head["launches"] * args.steps,  # counted by the library (nerf_timing.kernel_launches) per step
+            "parity": parity,
             "clocks": clk,
             "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": n_rays * 12},
@@ -322,32 +387,40 @@ def gpu_arm(args):
             "e2e_many": None if many_ms is None else {
                 "value": 4 * n_rays / (many_ms * 1e-3), "unit": "rays/s", "views": 4,
                 "api": "nerf_render_many (pinned double buffer, copies overlap the next view)"},
-            "roofline": {"bound": "tensor", "kernel": {"fp16x3": "mlp_tc_x3_kernel (fine pass; 3 MMAs per product, credited once)",
-                                                       "fp32": "mlp_fp32_kernel (fine pass; CUDA cores)"}.get(
-                             args.precision, "mlp_tc_kernel (fine pass)"), "achieved": ach, "peak": sustained,
-                         "unit": "TFLOP/s", "frac": ach / sustained, "peak_kind": f"bf16 sustained, {kind}",
-                         "frac_of_burst": ach / burst,
-                         # DRAM bytes of the fine-pass launch of one full frame (ncu --set full, read + write,
-                         # profiles/r01_mlp_tc_v15_ncu_full_summary.csv), scaled to this rank's share of the rays
-                         "traffic": NCU_FINE_DRAM_GB * n_local / n_rays if args.precision in ("fp16", "bf16", "mixed") else None, "traffic_unit": "GB per launch (ncu dram read+write)"},
+            # the kernel with the largest stage time on rank 0; `frame` is the whole step against the same peak
+            "roofline": {"bound": "tensor", "kernel": fine_kernel if dominant_is_fine else coarse_kernel,
+                         "achieved": ach if dominant_is_fine else c_ach, "peak": sustained, "unit": "TFLOP/s",
+                         "frac": (ach if dominant_is_fine else c_ach) / sustained, "peak_kind": f"bf16 sustained, {kind}",
+                         "frac_of_burst": (ach if dominant_is_fine else c_ach) / burst,
+                         "flop_per_sample": FLOP_FINE if dominant_is_fine else FLOP_COARSE,
+                         "stage_ms": mf if dominant_is_fine else mc,
+                         "frame": {"achieved": frame_tflops, "frac": frame_tflops / sustained / world,
+                                   "frac_of_burst": frame_tflops / burst / world,
+                                   "note": "algorithmic FLOP of the whole step / step time / (peak x n_gpus)"},
+                         "traffic": (NCU_FINE_DRAM_GB * n_local / n_rays
+                                     if dominant_is_fine and args.precision in ("fp16", "bf16", "mixed") else None),
+                         "traffic_unit": "GB per launch",
+                         "traffic_source": f"constant from one ncu --set full capture ({NCU_FINE_DRAM_SOURCE}, dram read + "
+                                           "write of the fine-pass launch), scaled to this rank's share of the rays; not "
+                                           "measured by this run"},
+            "roofline_other": {"bound": "tensor", "kernel": coarse_kernel if dominant_is_fine else fine_kernel,
+                               "achieved": c_ach if dominant_is_fine else ach, "peak": sustained, "unit": "TFLOP/s",
+                               "frac": (c_ach if dominant_is_fine else ach) / sustained,
+                               "stage_ms": mc if dominant_is_fine else mf,
+                               "note": "credited FLOP (one product per MAC); the split-operand kernel executes three"},
         }
-        if args.precision in ("mixed", "fp16x3"):
-            c_ach = n_local * NC * FLOP_COARSE / (mc * 1e-3) / 1e12
-            line["roofline_coarse"] = {
-                "bound": "tensor", "kernel": "mlp_tc_x3_kernel (coarse pass, sigma only; executes 3 MMAs per product, credited once)",
-                "achieved": c_ach, "executed": 3 * c_ach, "peak": sustained, "unit": "TFLOP/s", "frac": c_ach / sustained,
-                "frac_of_burst": c_ach / burst, "executed_frac_of_burst": 3 * c_ach / burst}
         if world == 1 and not args.no_cpu:
             O, ctx, cores, begin, n = cpu_sample()
             band = []
             dt = run_cpu_step((O, ctx), cores, begin, n, keep=band)
             # BASELINE.json's metric ends "PSNR vs ref": the rows the CPU arm just rendered against the same rows of the
             # frame the e2e leg left in host memory (identical deterministic sample positions on both sides)
-            d = np.abs(pinned.numpy()[begin:begin + n] - band[0])
-            line["parity"] = {"vs": "CPU oracle (the reference's algorithm restated), same rays, same sample positions",
-                              "rays": n, "max_abs_diff_x255": float(d.max() * 255.0),
-                              "pixels_over_2_255": int((d.max(axis=1) > 2.0 / 255.0).sum()),
-                              "psnr_db": float(10.0 * np.log10(1.0 / max(float(np.mean(d.astype(np.float64) ** 2)), 1e-20)))}
+            d = np.abs(host_copy[begin:begin + n] - band[0])
+            line["parity_live_band"] = {
+                "vs": "CPU oracle run just now on this box, same rays, same sample positions",
+                "rays": n, "max_abs_diff_x255": float(d.max() * 255.0),
+                "pixels_over_2_255": int((d.max(axis=1) > 2.0 / 255.0).sum()),
+                "psnr_db": float(10.0 * np.log10(1.0 / max(float(np.mean(d.astype(np.float64) ** 2)), 1e-20)))}
             line["cpu_baseline"] = {"value": n / dt, "unit": "rays/s", "cores": cores, "kind": "port",
                                     "sample": f"{n} rays of the same frame (pixel indices {begin}..{begin + n}), "
                                               f"{dt:.1f} s, oracle reordered bit-identical GEMM loop"}
@@ -360,6 +433,11 @@ def gpu_arm(args):
         dist.barrier()
         if rank == 0:
             sf.close()
+    if shm_path is not None:
+        torch.cuda.cudart().cudaHostUnregister(host_frame.ctypes.data)
+        dist.barrier()
+        if rank == 0:
+            os.unlink(shm_path)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -27,6 +27,12 @@ struct TcWeights {
   TcConsts consts;
 };
 
+// Names the layout of the pre-swizzled chunk streams (both kernels).  CHANGE IT whenever the chunk order, the N split
+// between the CTAs of a pair, the K-block size, the swizzle or the hi/lo scaling changes: weight cache files carry its
+// hash in their version word (weight_cache.cu) and files of another layout are refused.
+constexpr char kTcLayoutTag[] =
+    "r2:kmajor-sw128;kblock64;n256(viewdirs128);order=d0:pe|d1-4:4|d5:pe+4|d6-7:4|bott:4|view:4+pe4;x3=hi,lo*2^11 per kblock";
+
 // Operand formats: 0 = bf16, 1 = fp16 (mlp_tc.cu), 2 = fp16 hi / lo split, a hi and a lo chunk per K-block (mlp_tc_x3.cu).
 constexpr int kNumTcFormats = 3;
 // Host side (no GPU needed): the chunk stream of one network in one format, and the epilogue's f32 tables.

@@ -18,7 +18,15 @@ namespace nerf {
 namespace {
 
 constexpr char kMagic[8] = {'N', 'R', 'F', 'B', '2', '0', '0', 'W'};
-constexpr uint32_t kVersion = 1;
+// File version = format revision (high 8 bits) | a hash of kTcLayoutTag (mlp_tc.h): the chunk streams are shared-memory
+// images of one kernel generation, and a file written for another chunk order or swizzle has the right size and a
+// valid checksum - it must be refused, not rendered.
+constexpr uint32_t fnv1a24(const char* s) {
+  uint32_t h = 2166136261u;
+  while (*s) h = (h ^ (uint32_t)(unsigned char)*s++) * 16777619u;
+  return (h ^ (h >> 24)) & 0xffffffu;
+}
+constexpr uint32_t kVersion = (2u << 24) | fnv1a24(kTcLayoutTag);
 
 uint64_t fnv1a(const uint8_t* p, size_t n) {
   uint64_t h = 1469598103934665603ull;

@@ -99,6 +99,8 @@ class SharedFrame:
                     srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
                     srv.bind(path)
                     srv.listen(self.world)
+                    srv.settimeout(60.0)  # a rank that died before connecting must not hang the job: accept() raises,
+                    #                       the caller's all_reduce(MIN) then moves every rank to the NCCL gather
                 info = [(path, size.value)]
             else:
                 info = [("error: " + L.nerf_last_error().decode(), 0)]
@@ -121,6 +123,7 @@ class SharedFrame:
                 os.close(fd)  # the mapping keeps the allocation alive
         else:
             cli = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            cli.settimeout(60.0)
             cli.connect(path)
             _, fds, _, _ = socket.recv_fds(cli, 16, 1)
             cli.close()

@@ -1,0 +1,165 @@
+"""GPU tests added in round 2 (all through the C ABI, against the CPU oracle or against the library's own
+slower-but-simpler path where the claim is bit-identity):
+
+  - the WHOLE 800x800 frame of every mode against the oracle's frame (tests/golden/frame_800.npz) - the north star's
+    image criterion "against the reference render" (render_image, src/lib.rs:474-565) on all 640 000 pixels;
+  - the product default (Philox jitter + mixed precision) at the reference's sample counts against the oracle;
+  - the mixed mode's two-pass coarse densities == the split-operand kernel over every coarse sample, bit for bit;
+  - renders cut into chunks == the single-chunk render, bit for bit, in every sampling mode;
+  - two calls on two streams == the same calls one after the other.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle as O
+import nerf_rs_b200 as nb
+
+from .conftest import DATA
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _psnr(a, b):
+    return 10 * np.log10(1.0 / max(float(np.mean((a.astype(np.float64) - b) ** 2)), 1e-20))
+
+
+def _frame800():
+    """tests/golden/frame_800.npz (made by tests/golden/make_frame800.py): background mask + the other pixels."""
+    z = np.load(os.path.join(HERE, "golden", "frame_800.npz"))
+    n = int(z["W"]) * int(z["H"])
+    white = np.unpackbits(z["white"])[:n].astype(bool)
+    frame = np.ones((n, 3), np.float32)
+    frame[~white] = z["rgb"]
+    return frame
+
+
+# Pixels of the 800x800 frame that may differ from the oracle by more than 2/255, per mode.  The reference's pipeline is
+# discontinuous in its own rounding (a fine sample falls on one side or the other of a sliver of density, DESIGN.md
+# 4.3), so even the order-faithful f32 kernel - same sums in the same order, sinf/expf within 2 ulp of glibc - may
+# land a pixel elsewhere; the bounds below are what was measured plus slack, and the single-pass modes are recorded, not
+# hidden.
+FRAME_BOUNDS = {  # mode: (pixels > 2/255 allowed, PSNR floor in dB)
+    "fp32": (2, 90.0), "fp16x3": (2, 85.0), "mixed": (2, 80.0), "fp16": (300, 60.0), "bf16": (12000, 45.0)}
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp16x3", "mixed", "fp16", "bf16"])
+def test_full_800_frame_against_the_oracle(renderer, cam, prec):
+    want = _frame800()
+    got = renderer.render_image(cam, 800, 800, 64, 128, precision=prec)
+    assert got.shape == want.shape and np.isfinite(got).all()
+    d = np.abs(got - want).max(axis=1)
+    bad = int((d > 2.0 / 255.0).sum())
+    psnr = _psnr(got, want)
+    print(f"800x800 frame vs oracle, {prec}: max {d.max() * 255:.3f}/255, pixels > 2/255: {bad} of {d.size}, "
+          f"> 1/255: {int((d > 1.0 / 255.0).sum())}, PSNR {psnr:.2f} dB")
+    allowed, floor = FRAME_BOUNDS[prec]
+    assert psnr >= 45.0 and psnr >= floor, (prec, psnr)
+    assert bad <= allowed, (prec, bad, float(d.max()) * 255)
+    # white background exactly where the oracle has it: zero density along the whole ray on both sides
+    if prec in ("fp32", "fp16x3", "mixed"):
+        white_o = np.all(want == 1.0, axis=1)
+        white_g = np.all(got == 1.0, axis=1)
+        assert (white_o != white_g).mean() < 2e-3
+
+
+@pytest.mark.parametrize("prec,tol", [("mixed", 2.0), ("fp32", 1.0)])
+def test_philox_default_sampling_at_reference_counts(renderer, cam, onets, ocam, prec, tol):
+    """The CLI's and the mirrors' default: Philox jitter, 64 + 128 samples, mixed precision.  Jittered coarse samples
+    and random u make the merge unsorted-by-construction paths run (bitonic sort of the fine samples)."""
+    W = H = 64
+    want = O.render(onets[0], onets[1], ocam, W, H, 64, 128, mode=O.SAMPLING_PHILOX, seed=5)
+    got = renderer.render_image(cam, W, H, 64, 128, precision=prec, mode=nb.SAMPLING_PHILOX, seed=5)
+    d = np.abs(got - want).max(axis=1)
+    print(f"philox 64x64 {prec}: max {d.max() * 255:.3f}/255, PSNR {_psnr(got, want):.1f} dB")
+    assert d.max() * 255 <= tol and _psnr(got, want) >= 60.0
+    other = renderer.render_image(cam, W, H, 64, 128, precision=prec, mode=nb.SAMPLING_PHILOX, seed=6)
+    assert np.abs(other - got).max() > 1e-4  # the seed matters
+
+
+def _fresh(env):
+    keys = ("NERF_B200_COARSE_SELECT", "NERF_B200_CHUNK_RAYS", "NERF_B200_SELECT_MARGIN", "NERF_B200_SELECT_TAU")
+    saved = {k: os.environ.pop(k, None) for k in keys}
+    os.environ.update(env)
+    try:
+        return nb.Renderer(DATA, device=0)
+    finally:
+        for k in keys:
+            os.environ.pop(k, None)
+            if saved[k] is not None:
+                os.environ[k] = saved[k]
+
+
+def test_two_pass_coarse_equals_split_operands_everywhere(renderer, cam):
+    """mixed mode: fp16 over every coarse sample + split operands over the samples that can reach a coarse weight must
+    give the frame the split-operand kernel over EVERY coarse sample gives - same fine sample positions, same pixels."""
+    full = _fresh({"NERF_B200_COARSE_SELECT": "0"})
+    try:
+        W = H = 200
+        for mode, seed in ((nb.SAMPLING_DET, 0), (nb.SAMPLING_PHILOX, 3)):
+            a, sa = full.render_image(cam, W, H, 64, 128, precision="mixed", mode=mode, seed=seed, stages=True)
+            b, sb = renderer.render_image(cam, W, H, 64, 128, precision="mixed", mode=mode, seed=seed, stages=True)
+            assert (sa["w_c"] == sb["w_c"]).all() and (sa["t_f"] == sb["t_f"]).all() and (a == b).all()
+            t = renderer.timing()
+            assert t["coarse_samples"] == W * H * 64 and 0 < t["coarse_refined"] < 0.5 * t["coarse_samples"]
+            # the densities that were not re-evaluated are zero or lie behind an opaque stretch of the ray
+            diff = sa["sigma_c"] != sb["sigma_c"]
+            assert (sb["w_c"][diff] == 0).all()
+        # ray ranges of the two-pass path equal the same rows of its full frame (what multi-GPU sharding relies on)
+        det = renderer.render_image(cam, W, H, 64, 128, precision="mixed")
+        part = renderer.render_image(cam, W, H, 64, 128, precision="mixed", ray_begin=12345, ray_end=23456)
+        assert (part == det[12345:23456]).all()
+    finally:
+        full.close()
+
+
+def test_chunked_render_equals_single_chunk(renderer, cam):
+    """Frames above chunk_rays rays (every 1600x1600 orbit frame) are rendered in chunks; offsets of the jitter / u
+    arrays, Philox pixel indices and output rows must not depend on the chunking (chunk of 40 rays, not a divisor)."""
+    small = _fresh({"NERF_B200_CHUNK_RAYS": "40"})
+    try:
+        W, H, nc, nf = 24, 16, 16, 24
+        n = W * H
+        rng = np.random.default_rng(8)
+        jit = rng.uniform(0, 1, (n, nc)).astype(np.float32)
+        u = rng.uniform(0, 1, (n, nf)).astype(np.float32)
+        for prec in ("fp32", "mixed"):
+            for kw in (dict(mode=nb.SAMPLING_DET), dict(mode=nb.SAMPLING_PHILOX, seed=9),
+                       dict(mode=nb.SAMPLING_ARRAYS, jitter=jit, u=u)):
+                a = renderer.render_image(cam, W, H, nc, nf, precision=prec, **kw)
+                b = small.render_image(cam, W, H, nc, nf, precision=prec, **kw)
+                assert (a == b).all(), (prec, kw["mode"])
+                a = renderer.render_image(cam, W, H, nc, nf, precision=prec, ray_begin=31, ray_end=333, **(
+                    kw if kw["mode"] != nb.SAMPLING_ARRAYS else dict(mode=nb.SAMPLING_ARRAYS, jitter=jit[31:333], u=u[31:333])))
+                b = small.render_image(cam, W, H, nc, nf, precision=prec, ray_begin=31, ray_end=333, **(
+                    kw if kw["mode"] != nb.SAMPLING_ARRAYS else dict(mode=nb.SAMPLING_ARRAYS, jitter=jit[31:333], u=u[31:333])))
+                assert (a == b).all(), (prec, kw["mode"], "range")
+        ra, da, aa = renderer.render_aux(cam, W, H, nc, nf, precision="fp32")
+        rb, db, ab = small.render_aux(cam, W, H, nc, nf, precision="fp32")
+        assert (ra == rb).all() and (da == db).all() and (aa == ab).all()
+        assert (small.render_rgb8(cam, W, H, nc, nf, precision="fp16") == renderer.render_rgb8(cam, W, H, nc, nf, precision="fp16")).all()
+    finally:
+        small.close()
+
+
+def test_two_streams_on_one_context_do_not_overlap(renderer, cam):
+    """A context has one set of workspaces: a *_device call on a second stream must wait (on the device) for the call
+    before it.  Two different renders enqueued back to back on two streams, then compared with the serial results."""
+    import torch
+    W, H = 96, 64
+    n = W * H
+    want_a = renderer.render_image(cam, W, H, 64, 128, precision="mixed")
+    want_b = renderer.render_image(cam, W, H, 64, 128, precision="mixed", mode=nb.SAMPLING_PHILOX, seed=2)
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    out_a = torch.zeros(n, 3, device="cuda:0")
+    out_b = torch.zeros(n, 3, device="cuda:0")
+    torch.cuda.synchronize()
+    for _ in range(3):
+        renderer.render_device(cam, W, H, out_a.data_ptr(), 64, 128, precision="mixed", stream=s1.cuda_stream)
+        renderer.render_device(cam, W, H, out_b.data_ptr(), 64, 128, precision="mixed", mode=nb.SAMPLING_PHILOX, seed=2,
+                               stream=s2.cuda_stream)
+    torch.cuda.synchronize()
+    assert (out_a.cpu().numpy() == want_a).all() and (out_b.cpu().numpy() == want_b).all()

@@ -276,7 +276,9 @@ def test_weight_cache_file_is_deterministic_and_checked(tmp_path):
     nb.build_weight_cache(DATA, b)
     raw = open(a, "rb").read()
     assert raw == open(b, "rb").read()
-    assert raw[:8] == b"NRFB200W" and struct.unpack_from("<II", raw, 8) == (1, 2)
+    version, n_nets = struct.unpack_from("<II", raw, 8)
+    assert raw[:8] == b"NRFB200W" and n_nets == 2
+    assert version >> 24 == 2 and version & 0xffffff != 0  # format revision | hash of the chunk-stream layout tag
     # two nets x (f32 tensors + bf16 + fp16 + split-fp16 streams): 2 x (2 383 376 + 1 196 032 x 4) B + names / dims
     assert 2 * (2383376 + 4 * 1196032) < len(raw) < 2 * (2383376 + 4 * 1196032) + 4096
     w = np.fromfile(os.path.join(DATA, "fine", "dense5_kernel.bin"), np.float32)
@@ -295,6 +297,19 @@ def test_weight_cache_file_is_deterministic_and_checked(tmp_path):
         assert L.nerf_create_from_cache(os.fsencode(path), 0, C.byref(h)) == nb.E_IO, name
         assert b"weight cache" in L.nerf_last_error()
     assert L.nerf_create_from_cache(os.fsencode(str(tmp_path / "missing")), 0, C.byref(h)) == nb.E_IO
+    # a file written for another chunk-stream layout (an older kernel generation): same size, valid checksum, other
+    # layout hash in the version word -> refused, never rendered
+    def fnv1a64(b):
+        hsh = 1469598103934665603  # weight_cache.cu::fnv1a
+        for x in np.frombuffer(b, np.uint8).tolist():
+            hsh = ((hsh ^ x) * 0x100000001b3) & 0xffffffffffffffff
+        return hsh
+    small = bytearray(raw[:8] + struct.pack("<II", version ^ 0x5a5a, 2))
+    small += struct.pack("<Q", fnv1a64(bytes(small)))
+    path = str(tmp_path / "other_layout")
+    open(path, "wb").write(bytes(small))
+    assert L.nerf_create_from_cache(os.fsencode(path), 0, C.byref(h)) == nb.E_UNSUPPORTED
+    assert b"unsupported version" in L.nerf_last_error()
     # an intact file gets as far as the device: no GPU here, no CPU fallback
     from tests.conftest import _have_gpu
     if not _have_gpu():
