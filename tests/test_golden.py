@@ -89,3 +89,26 @@ def test_gpu_800_band_against_the_oracle(renderer, cam):
     mx, psnr = err("fp16")
     print(f"800-band vs oracle, fp16: max {mx:.3f}/255, PSNR {psnr:.1f} dB")
     assert psnr >= 45.0 and mx > 2.0, ("fp16", mx, psnr)  # documented behaviour, see DESIGN.md 4.3
+
+
+def _frame800():
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "frame_800.npz"))
+    n = int(z["W"]) * int(z["H"])
+    white = np.unpackbits(z["white"])[:n].astype(bool)
+    frame = np.ones((n, 3), np.float32)
+    frame[~white] = z["rgb"]
+    return z, frame
+
+
+def test_oracle_reproduces_full_frame_fixture(onets, ocam):
+    """Drift guard for tests/golden/frame_800.npz (the oracle's whole 800x800 frame, tests/golden/make_frame800.py):
+    the stored hash, its rows 200..207 against the older band fixture, and three 64-ray strips re-rendered now."""
+    import hashlib
+    z, frame = _frame800()
+    assert hashlib.sha256(frame.tobytes()).hexdigest() == str(z["sha256"])
+    assert np.array_equal(frame[int(B800["ray_begin"]):int(B800["ray_end"])], B800["rgb"])
+    assert 0.70 < float(np.all(frame == 1.0, axis=1).mean()) < 0.75  # background: zero density along the whole ray
+    for row, col in ((120, 400), (430, 300), (700, 520)):
+        rb = row * 800 + col
+        rgb = O.render(onets[0], onets[1], ocam, 800, 800, 64, 128, ray_begin=rb, ray_end=rb + 64)
+        assert np.abs(rgb - frame[rb:rb + 64]).max() <= 2e-6
