@@ -1,0 +1,125 @@
+//! ffi.rs — the C ABI of libnerf_b200.so (include/nerf_b200.h), declared by hand: one `extern` per entry point the
+//! crate binds.  Struct layouts mirror the header's (`#[repr(C)]`).
+use std::ffi::CStr;
+use std::os::raw::{c_char, c_int, c_void};
+
+#[repr(C)]
+pub struct NerfCtx {
+    _opaque: [u8; 0],
+}
+
+/// nerf_camera: struct Camera after camera_from_samples (lib.rs:197-211,614-645).
+#[repr(C)]
+#[derive(Clone, Copy, Debug)]
+pub struct NerfCamera {
+    pub origin: [f32; 3],
+    pub forward: [f32; 3],
+    pub up: [f32; 3],
+    pub alpha_w: f32,
+    pub alpha_h: f32,
+    pub near: f32,
+    pub far: f32,
+}
+
+/// nerf_sampling: mode 0 = deterministic, 1 = Philox(seed, pixel, stream), 2 = caller arrays.
+#[repr(C)]
+pub struct NerfSampling {
+    pub mode: i32,
+    pub seed: u64,
+    pub jitter: *const f32,
+    pub u: *const f32,
+}
+
+#[repr(C)]
+pub struct NerfTensor {
+    pub name: *const c_char,
+    pub ndim: i32,
+    pub dims: [i64; 2],
+    pub data: *const f32,
+}
+
+// nerf_precision
+pub const PREC_FP32: c_int = 0;
+pub const PREC_BF16: c_int = 1;
+pub const PREC_FP16: c_int = 2;
+pub const PREC_FP16X3: c_int = 4;
+pub const PREC_MIXED: c_int = 5;
+pub const NET_COARSE: c_int = 0;
+pub const NET_FINE: c_int = 1;
+
+extern "C" {
+    pub fn nerf_last_error() -> *const c_char;
+    pub fn nerf_create(root: *const c_char, device: c_int, out: *mut *mut NerfCtx) -> c_int;
+    pub fn nerf_create_from_tensors(
+        coarse: *const NerfTensor,
+        n_coarse: c_int,
+        fine: *const NerfTensor,
+        n_fine: c_int,
+        device: c_int,
+        out: *mut *mut NerfCtx,
+    ) -> c_int;
+    pub fn nerf_create_from_cache(cache: *const c_char, device: c_int, out: *mut *mut NerfCtx) -> c_int;
+    pub fn nerf_build_weight_cache(root: *const c_char, cache: *const c_char) -> c_int;
+    pub fn nerf_destroy(ctx: *mut NerfCtx);
+    pub fn nerf_forward_batch(
+        ctx: *mut NerfCtx,
+        net: c_int,
+        points: *const f32,
+        dirs: *const f32,
+        batch: i64,
+        precision: c_int,
+        rgb: *mut f32,
+        sigma: *mut f32,
+    ) -> c_int;
+    pub fn nerf_render(
+        ctx: *mut NerfCtx,
+        cam: *const NerfCamera,
+        w: c_int,
+        h: c_int,
+        n_coarse: c_int,
+        n_fine: c_int,
+        precision: c_int,
+        smp: *const NerfSampling,
+        ray_begin: i64,
+        ray_end: i64,
+        rgb: *mut f32,
+    ) -> c_int;
+    pub fn nerf_render_rgb8(
+        ctx: *mut NerfCtx,
+        cam: *const NerfCamera,
+        w: c_int,
+        h: c_int,
+        n_coarse: c_int,
+        n_fine: c_int,
+        precision: c_int,
+        smp: *const NerfSampling,
+        ray_begin: i64,
+        ray_end: i64,
+        channels: c_int,
+        out: *mut u8,
+    ) -> c_int;
+    pub fn nerf_render_device(
+        ctx: *mut NerfCtx,
+        cam: *const NerfCamera,
+        w: c_int,
+        h: c_int,
+        n_coarse: c_int,
+        n_fine: c_int,
+        precision: c_int,
+        smp: *const NerfSampling,
+        ray_begin: i64,
+        ray_end: i64,
+        d_rgb: *mut f32,
+        stream: *mut c_void,
+    ) -> c_int;
+    pub fn nerf_camera_from_json(path: *const c_char, out: *mut NerfCamera) -> c_int;
+    pub fn nerf_save_ppm(path: *const c_char, w: c_int, h: c_int, rgb: *const f32) -> c_int;
+}
+
+/// The reference panics on every error (lib.rs:36,118,483-501); so does the shim, with the library's message.
+pub fn check(rc: c_int, what: &str) {
+    if rc != 0 {
+        let msg = unsafe { CStr::from_ptr(nerf_last_error()) }.to_string_lossy().into_owned();
+        panic!("{what}: {msg}");
+    }
+}

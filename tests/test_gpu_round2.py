@@ -165,3 +165,20 @@ def test_two_streams_on_one_context_do_not_overlap(renderer, cam):
                                stream=s2.cuda_stream)
     torch.cuda.synchronize()
     assert (out_a.cpu().numpy() == want_a).all() and (out_b.cpu().numpy() == want_b).all()
+
+
+@pytest.mark.parametrize("prec", ["mixed", "fp32"])
+def test_pr1_reference_output_ppm(renderer, cam, prec):
+    """BASELINE.json configs[0]: the reference's own run (render_cli_image, lib.rs:647-677: 256x256, 64 + 128 samples,
+    output.ppm) as the CPU oracle wrote it with deterministic sampling (scripts/pr1_reference.py ->
+    tests/golden/pr1_output_det_256.ppm).  The GPU frame through the device-side save_ppm quantiser: same header, every
+    byte within 1 of the oracle's, almost all identical."""
+    want = open(os.path.join(HERE, "golden", "pr1_output_det_256.ppm"), "rb").read()
+    head = b"P6\n256 256\n255\n"
+    assert want.startswith(head) and len(want) == len(head) + 256 * 256 * 3
+    got = renderer.render_rgb8(cam, 256, 256, 64, 128, precision=prec).tobytes()
+    a = np.frombuffer(want[len(head):], np.uint8).astype(np.int16)
+    b = np.frombuffer(got, np.uint8).astype(np.int16)
+    d = np.abs(a - b)
+    print(f"PR1 256x256 output.ppm, {prec}: bytes differing {int((d > 0).sum())} of {d.size}, max {int(d.max())}")
+    assert d.max() <= 2 and (d > 1).sum() <= 3 and (d > 0).mean() < 0.02

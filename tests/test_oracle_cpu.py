@@ -330,3 +330,29 @@ def test_shared_frame_entry_points_reject_bad_arguments():
     assert L.nerf_shared_frame_open_fd(None, 3, 1024, C.byref(p)) == nb.E_ARG
     assert L.nerf_shared_frame_close_fd(None, None) == 0
     assert b"bad argument" in L.nerf_last_error()
+
+
+def test_rust_shim_binds_only_exported_symbols():
+    """rust/ cannot be compiled here (no cargo / rustc); what can be checked is that every `extern "C"` function its
+    ffi.rs declares is a symbol libnerf_b200.so exports and include/nerf_b200.h declares, and that the crate has the
+    reference's file layout (Cargo.toml, build.rs, src/{lib,main,network,vec3,weights}.rs)."""
+    import re
+    import ctypes as C
+    import nerf_rs_b200 as nb
+    root = os.path.join(os.path.dirname(DATA.rstrip("/")), "..", "rust")
+    for rel in ("Cargo.toml", "build.rs", "README.md", "src/lib.rs", "src/main.rs", "src/network.rs", "src/vec3.rs",
+                "src/weights.rs", "src/ffi.rs"):
+        assert os.path.exists(os.path.join(root, rel)), rel
+    ffi = open(os.path.join(root, "src", "ffi.rs")).read()
+    names = set(re.findall(r"pub fn (nerf_\w+)\s*\(", ffi))
+    assert {"nerf_create", "nerf_forward_batch", "nerf_render", "nerf_save_ppm", "nerf_create_from_tensors"} <= names
+    header = open(os.path.join(root, "..", "include", "nerf_b200.h")).read()
+    L = C.CDLL(nb.LIB_PATH)
+    for n in names:
+        assert n in nb.EXPORTS and re.search(r"\b%s\s*\(" % n, header), n
+        getattr(L, n)
+    cargo = open(os.path.join(root, "Cargo.toml")).read()
+    assert 'build = "build.rs"' in cargo and 'crate-type = ["rlib", "cdylib"]' in cargo and 'name = "nerf-rs"' in cargo
+    # precision constants of the shim == the header's enum
+    for name, val in re.findall(r"pub const PREC_(\w+): c_int = (\d+);", ffi):
+        assert re.search(r"NERF_PREC_%s = %s\b" % (name, val), header), name
