@@ -83,6 +83,7 @@ struct nerf_ctx {
   // two-pass coarse densities of the mixed mode: ids of the samples the split-operand kernel re-evaluates
   DevBuf sel_list, sel_count;
   bool coarse_select = true;    // NERF_B200_COARSE_SELECT=0: split-operand kernel over every coarse sample
+  bool skip_empty = true;       // NERF_B200_SKIP_EMPTY=0: the fine pass evaluates the colour of empty samples too
   // NERF_B200_SELECT_MARGIN: bound on the fp16 pass's pre-activation error near zero.  Measured (scripts/select_check.py,
   // 800x800 reference pose): the frame stays bit-identical down to 0.03, so 0.5 keeps a factor 16.
   float select_margin = 0.5f;
@@ -202,6 +203,7 @@ int create_common(const TensorMap& coarse, const TensorMap& fine, int device, ne
     if (v > 0) ctx->chunk_rays = v;
   }
   if (const char* e = std::getenv("NERF_B200_COARSE_SELECT")) ctx->coarse_select = std::atoi(e) != 0;
+  if (const char* e = std::getenv("NERF_B200_SKIP_EMPTY")) ctx->skip_empty = std::atoi(e) != 0;
   if (const char* e = std::getenv("NERF_B200_SELECT_MARGIN")) ctx->select_margin = (float)std::atof(e);
   if (const char* e = std::getenv("NERF_B200_SELECT_TAU")) ctx->select_tau = (float)std::atof(e);
   cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
@@ -402,7 +404,7 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
     src.S = nm;
     src.B = n * nm;
     src.t = c->tf.as<float>();
-    dst = SampleDst{c->sigf.as<float>(), c->rgbf.as<float>()};
+    dst = SampleDst{c->sigf.as<float>(), c->rgbf.as<float>(), 0.0f, c->skip_empty ? 1 : 0};
     span_begin(c, ST_MLP_FINE, s);
     rc = run_mlp(c, NERF_NET_FINE, src, dst, precision, s);
     span_end(c, s);
@@ -741,12 +743,15 @@ static int render_host(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc
   if ((rc = c->out.reserve(n * 12))) return rc;
   const bool want_stages = st != nullptr;
   const int64_t saved_chunk = c->chunk_rays;
+  const bool saved_skip = c->skip_empty;
   if (want_stages) c->chunk_rays = n;  // stage dumps read the workspaces of a single chunk
+  if (want_stages && st->rgb_f) c->skip_empty = false;  // a caller who asks for every sample's colour gets it
   timing_start(c, s);
   rc = render_range(c, *cam, W, H, nc, nf, precision, mode, smp ? smp->seed : 0, d_jit, d_u, rb, re,
                     c->out.as<float>(), want_stages && st->w_c, s);
   timing_stop(c, s);
   c->chunk_rays = saved_chunk;
+  c->skip_empty = saved_skip;
   if (rc != NERF_OK) return rc;
   NERF_CUDA(cudaMemcpyAsync(rgb, c->out.p, n * 12, cudaMemcpyDeviceToHost, s));
   if (want_stages) {

@@ -57,6 +57,9 @@ struct SampleDst {
   // sigma = max(alpha(h8), sigma_floor): 0 is the reference's ReLU (network.rs:216, fmaxf also maps NaN to 0);
   // -inf stores the pre-activation itself (first pass of the two-pass coarse densities)
   float sigma_floor;
+  // 1: samples whose density is 0 get rgb = 0 instead of the network's colour (their compositing weight is exactly 0,
+  // lib.rs:176-195); lets the fused kernel skip the colour branch where a whole tile is empty.  Render launches only.
+  int skip_empty_rgb;
 };
 
 // Camera constants hoisted out of get_ray_dir (lib.rs:216-226): they do not depend on the pixel, so

@@ -52,8 +52,11 @@ constexpr uint32_t kOffAct = 0;
 constexpr uint32_t kOffAux = kOffAct + 2 * kActBytes;
 constexpr uint32_t kOffStage = kOffAux + 2 * kAuxBytes;
 constexpr uint32_t kOffBar = kOffStage + kStages * kStageBytes;
-// barrier block, 8 B each: full[4] pfull[4] empty[4] acc[2] act[2] | tmem slot
+// barrier block, 8 B each: full[4] pfull[4] empty[4] acc[2] act[2] | tmem slot | flag[2] | flag words [2][8]
 constexpr uint32_t kBarFull = 0, kBarPFull = 32, kBarEmpty = 64, kBarAcc = 96, kBarAct = 112, kTmemSlotOff = 128;
+// kSkipEmpty: "does slot s need its colour branch" - one word per (CTA, row quadrant), written with st.async into the
+// leader CTA, whose flag[s] barrier counts the 8 x 4 bytes
+constexpr uint32_t kBarFlag = 136, kFlagWords = 160, kFlagBytes = 8 * 4;
 constexpr uint32_t kSmemBytes = kOffBar + 256;  // 224.25 KiB
 static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 constexpr int kLead = 4;  // chunks of a layer slot X issues before slot Y starts the same layer
@@ -196,7 +199,13 @@ __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t threads) {
 // kRawSigma: store the density head's pre-activation alpha(h8) instead of relu(alpha(h8)) (first pass of the two-pass
 // coarse densities).  A template parameter, not a run-time flag: reading one more kernel parameter in the epilogue
 // made ptxas spill two registers of the 112-register epilogue warps.
-template <bool kFp16, bool kRawSigma>
+// kSkipEmpty (render launches with colour): a sample with sigma = 0 has alpha = 0 and weight exactly 0 in
+// compute_weights / integrate_ray (lib.rs:176-195,250-283), so its colour cannot reach the pixel, and 73 % of the rays
+// of the lego frame have no density at all.  The MMA issuer skips the bottleneck and viewdirs MMAs of a slot in which no
+// row of either CTA has density; the weight chunks still stream and are released unread, and the epilogue drains the
+// stale accumulator (finite values: the colour stored for such samples is arbitrary but finite, and never used).
+// forward_batch never skips: the reference returns the colour of every sample.
+template <bool kFp16, bool kRawSigma, bool kSkipEmpty>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ chunks, const SampleSrc src,
               const SampleDst dst, unsigned long long* __restrict__ trace) {
@@ -228,6 +237,7 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_acc + 8 * s, 1);
       mbar_init(bar_act + 8 * s, 32);   // leader only: one elected arrive per epilogue warp, both CTAs
+      mbar_init(bar0 + kBarFlag + 8 * s, 1);  // leader only: the MMA issuer's own arrive.expect_tx; the stores complete the bytes
     }
     fence_barrier_init();
   }
@@ -300,8 +310,11 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
       const uint64_t act_desc0 = make_desc(base + kOffAct), aux_desc0 = make_desc(base + kOffAux);
       const uint64_t stage_desc0 = make_desc(base + kOffStage);
       uint32_t g0 = 0;       // ring index of the current layer's first chunk (the same for both slots)
-      uint32_t act_par = 0;  // bit s: parity of slot s's "layer input ready" barrier
+      // bit s: parity of slot s's "layer input ready" barrier; kSkipEmpty: bit 2 + s = slot s runs bottleneck + viewdirs
+      // in this quad, bit 4 + s = parity of slot s's colour-flag barrier (one word: uniform registers are scarce here)
+      uint32_t act_par = 0;
       for (int64_t quad = pair_id; quad < n_quads; quad += n_pairs) {
+        if (kSkipEmpty) act_par |= 12u;
 #pragma unroll 1
         for (int l = 0; l < n_layers; ++l) {
           const int nch = layer_chunks(l);
@@ -332,13 +345,28 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
               if (c == 0) {  // layer input written and accumulator drained (both CTAs)
                 mbar_wait(bar_act + 8 * s, (act_par >> s) & 1u);
                 act_par ^= 1u << s;
+                if (kSkipEmpty && l == 8) {  // the eight (CTA, row quadrant) verdicts on slot s's densities
+                  const uint32_t bar_flag = base + kOffBar + kBarFlag + 8u * (uint32_t)s;
+                  if (elect_one()) mbar_arrive_expect_tx(bar_flag, kFlagBytes);
+                  __syncwarp();
+                  mbar_wait_cluster(bar_flag, (act_par >> (4 + s)) & 1u);
+                  act_par ^= 16u << s;
+                  uint32_t any = 0;
+#pragma unroll
+                  for (uint32_t w = 0; w < 8; ++w)
+                    any |= ld_shared_u32(base + kOffBar + kFlagWords + (uint32_t)s * kFlagBytes + 4u * w);
+                  if (any == 0u) act_par &= ~(4u << s);
+                }
               }
+              const bool run = !kSkipEmpty || ((act_par >> (2 + s)) & 1u) != 0u;
               if (s == 0) mbar_wait(bar_pfull + 8 * stage, (g / kStages) & 1u);  // X is every chunk's first consumer
               tc_fence_after();
               tr.rec(0x100 | (l << 4) | c | (s << 12));
               const uint64_t bd = stage_desc0 + stage * (kStageBytes >> 4);
               if (elect_one()) {
-                if (c == aux_c) {
+                if (!run) {
+                  // nothing to multiply for this slot: the commits below still release the chunk and the epilogue
+                } else if (c == aux_c) {
                   tc_mma2_f16(d_tmem, auxd, bd, idesc, c != 0 ? 1u : 0u);
                   tc_mma2_f16(d_tmem, auxd + 2, bd + 2, idesc, 1u);
                   if (l != 9) {  // PE4(dir) is K = 32: aux columns 32..63 hold f32 scratch by then
@@ -395,7 +423,8 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
       fence_proxy_async();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(bar_act + 8 * s, 0u);  // one arrive per warp on the leader's barrier
+      if (elect_one()) mbar_arrive_cluster(bar_act + 8 * s, 0u);  // one arrive per warp on the leader's barrier (elected:
+      //                                                               keeping `lane` alive for this costs a register)
     };
 
     // The next quad's inputs are fetched two layers before they are needed: {p.xyz, -} for explicit points,
@@ -484,34 +513,49 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
           tc_fence_before();
         }
         float* scratch = reinterpret_cast<float*>(smem + kOffAux + s * kAuxBytes + scratch_off);
-        if (colq != 0) scratch[3] = sig[s];
+        if (kSkipEmpty || colq != 0) scratch[3] = sig[s];
       }
       named_bar_sync(row_bar, 128);
-      if (colq == 0) {
+      bool need[2] = {true, true};  // kSkipEmpty: some row of this warp has density in slot s (warp-uniform)
+      if (kSkipEmpty || colq == 0) {
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
           const uint8_t* aux = smem + kOffAux + s * kAuxBytes;
-          float v = sig[s];
+          float v = kSkipEmpty ? reinterpret_cast<const float*>(aux + sw128_offset(row, 32u))[3] : sig[s];
 #pragma unroll
           for (uint32_t k = 1; k < 4; ++k) v += reinterpret_cast<const float*>(aux + sw128_offset(row, 32u + 8u * k))[3];
-          if (valid[s]) dst.sigma[g[s]] = kRawSigma ? v : fmaxf(v, 0.0f);
+          if (colq == 0 && valid[s]) dst.sigma[g[s]] = kRawSigma ? v : fmaxf(v, 0.0f);
+          if constexpr (kSkipEmpty) {
+            // does any of this warp's 32 rows need slot s's colour?  Every quarter of a row block reaches the same
+            // verdict; quarter 0 sends it to the leader, one word per (CTA, row quadrant)
+            need[s] = __any_sync(0xffffffffu, valid[s] && v > 0.0f);
+            if (colq == 0 && elect_one())
+              st_async_u32(base + kOffBar + kFlagWords + (uint32_t)s * kFlagBytes + 4u * (rank * 4u + quad),
+                           need[s] ? 1u : 0u, base + kOffBar + kBarFlag + 8u * (uint32_t)s, 0u);
+          }
         }
       }
       if (want_rgb) {
 #pragma unroll
         for (int s = 0; s < 2; ++s) {  // bottleneck, ActivationType::None (network.rs:218)
           acc_wait(s);
-          epi_cols<kFp16, false, false, true>(tr, taddr0 + 256u * s, C.bias[8] + colq * 64, C.w_alpha, sig[s],
-                                              kblock_row0 + s * kActBytes, swz);
-          // PE4(dir) replaces PE10(p) in the aux tile (columns 0..31): the skip MMA that read it finished layers ago
-          uint8_t* aux_row = smem + kOffAux + s * kAuxBytes + (row >> 3) * 1024u + r8 * 128u;
-          if (colq == 0) write_pe16<kFp16, 0, kDirOctaves>(aux_row, r8, dir[s]);
-          else if (colq == 1) write_pe16<kFp16, 16, kDirOctaves>(aux_row, r8, dir[s]);  // columns 27..31: K padding
+          if (!kSkipEmpty || need[s]) {
+            epi_cols<kFp16, false, false, true>(tr, taddr0 + 256u * s, C.bias[8] + colq * 64, C.w_alpha, sig[s],
+                                                kblock_row0 + s * kActBytes, swz);
+            // PE4(dir) replaces PE10(p) in the aux tile (columns 0..31): the skip MMA that read it finished layers ago
+            uint8_t* aux_row = smem + kOffAux + s * kAuxBytes + (row >> 3) * 1024u + r8 * 128u;
+            if (colq == 0) write_pe16<kFp16, 0, kDirOctaves>(aux_row, r8, dir[s]);
+            else if (colq == 1) write_pe16<kFp16, 16, kDirOctaves>(aux_row, r8, dir[s]);  // columns 27..31: K padding
+          }
           act_ready(s);
         }
 #pragma unroll
         for (int s = 0; s < 2; ++s) {  // viewdirs (ReLU) then the f32 rgb head (network.rs:222-223): 32 columns per warp
           acc_wait(s);
+          if (kSkipEmpty && !need[s]) {  // nothing was multiplied for rows without density (or nothing worth reading)
+            tc_fence_before();
+            continue;
+          }
           uint32_t v[32];
           tc_ld32(tmem_base + ((quad * 32u) << 16) + 256u * s + 32u * (uint32_t)colq, v);
           tc_wait_ld();
@@ -541,6 +585,14 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
         if (colq == 0) {
 #pragma unroll
           for (int s = 0; s < 2; ++s) {
+            if (kSkipEmpty && !need[s]) {  // no density in these 32 rows: their colour is never looked at; keep it finite
+              if (valid[s]) {
+                dst.rgb[g[s] * 3 + 0] = 0.0f;
+                dst.rgb[g[s] * 3 + 1] = 0.0f;
+                dst.rgb[g[s] * 3 + 2] = 0.0f;
+              }
+              continue;
+            }
             const uint8_t* aux = smem + kOffAux + s * kAuxBytes;
             float r0 = sig[s], r1 = dir[s][0], r2 = dir[s][1];
 #pragma unroll
@@ -676,11 +728,14 @@ void free_tc_weights(TcWeights* w) {
 }
 
 cudaError_t init_mlp_tc() {  // once per process and device, at context creation
-  cudaError_t e = cudaFuncSetAttribute(mlp_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(mlp_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-  if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(mlp_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+  const void* kernels[5] = {(const void*)mlp_tc_kernel<true, true, false>, (const void*)mlp_tc_kernel<true, false, true>,
+                            (const void*)mlp_tc_kernel<true, false, false>, (const void*)mlp_tc_kernel<false, false, true>,
+                            (const void*)mlp_tc_kernel<false, false, false>};
+  for (const void* k : kernels) {
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
@@ -703,9 +758,15 @@ cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const Sample
   }
   const bool raw = dst.sigma_floor < 0.0f;
   if (raw && (w.fmt != 1 || dst.rgb != nullptr)) return cudaErrorInvalidValue;  // only the fp16 density-only pass has it
-  if (raw) mlp_tc_kernel<true, true><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace);
-  else if (w.fmt == 1) mlp_tc_kernel<true, false><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace);
-  else mlp_tc_kernel<false, false><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace);
+  const bool skip = dst.skip_empty_rgb != 0 && dst.rgb != nullptr;
+  const int which = raw ? 0 : (w.fmt == 1 ? (skip ? 1 : 2) : (skip ? 3 : 4));
+  switch (which) {
+    case 0: mlp_tc_kernel<true, true, false><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace); break;
+    case 1: mlp_tc_kernel<true, false, true><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace); break;
+    case 2: mlp_tc_kernel<true, false, false><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace); break;
+    case 3: mlp_tc_kernel<false, false, true><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace); break;
+    default: mlp_tc_kernel<false, false, false><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace); break;
+  }
   e = cudaGetLastError();
   if (trace != nullptr) {
     std::vector<unsigned long long> h(trace_bytes / 8);

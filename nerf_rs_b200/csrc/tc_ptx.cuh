@@ -70,6 +70,38 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) 
       "r"(cta)
       : "memory");
 }
+// Remote 4-byte store that reports its completion to an mbarrier of the destination CTA (complete_tx of 4 bytes):
+// `word` and `bar` are this CTA's shared-memory offsets of the objects at the same offsets in CTA `cta` of the cluster.
+// The waiter sees the value once the barrier phase (armed with expect_tx) completes; PTX as in CUTLASS
+// (cute/arch/cluster_sm90.hpp, store_shared_remote).
+__device__ __forceinline__ void st_async_u32(uint32_t word, uint32_t value, uint32_t bar, uint32_t cta) {
+  asm volatile(
+      "{\n\t.reg .b32 rw, rb;\n\t"
+      "mapa.shared::cluster.u32 rw, %0, %3;\n\t"
+      "mapa.shared::cluster.u32 rb, %2, %3;\n\t"
+      "st.async.shared::cluster.mbarrier::complete_tx::bytes.u32 [rw], %1, [rb];\n\t}" ::"r"(word),
+      "r"(value), "r"(bar), "r"(cta)
+      : "memory");
+}
+// Bounded wait with cluster-scope acquire: for barriers whose phase is completed by st.async stores from the peer CTA.
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  for (uint32_t spins = 0; !done; ++spins) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (spins > (1u << 22)) __trap();
+  }
+}
+__device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
 // one non-blocking probe of a barrier phase (arrivals may come from the peer CTA)
 __device__ __forceinline__ bool mbar_test_cluster(uint32_t bar, uint32_t parity) {
   uint32_t done;

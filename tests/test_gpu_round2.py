@@ -43,7 +43,7 @@ def _frame800():
 # land a pixel elsewhere; the bounds below are what was measured plus slack, and the single-pass modes are recorded, not
 # hidden.
 FRAME_BOUNDS = {  # mode: (pixels > 2/255 allowed, PSNR floor in dB)
-    "fp32": (2, 90.0), "fp16x3": (2, 85.0), "mixed": (2, 80.0), "fp16": (300, 60.0), "bf16": (12000, 45.0)}
+    "fp32": (2, 100.0), "fp16x3": (2, 95.0), "mixed": (2, 80.0), "fp16": (300, 60.0), "bf16": (4000, 50.0)}  # measured: 0 / 0 / 0 / 100 / 1 673 pixels; 119 / 108 / 90 / 71 / 59 dB
 
 
 @pytest.mark.parametrize("prec", ["fp32", "fp16x3", "mixed", "fp16", "bf16"])
@@ -83,7 +83,8 @@ def test_philox_default_sampling_at_reference_counts(renderer, cam, onets, ocam,
 
 
 def _fresh(env):
-    keys = ("NERF_B200_COARSE_SELECT", "NERF_B200_CHUNK_RAYS", "NERF_B200_SELECT_MARGIN", "NERF_B200_SELECT_TAU")
+    keys = ("NERF_B200_COARSE_SELECT", "NERF_B200_CHUNK_RAYS", "NERF_B200_SELECT_MARGIN", "NERF_B200_SELECT_TAU",
+            "NERF_B200_SKIP_EMPTY")
     saved = {k: os.environ.pop(k, None) for k in keys}
     os.environ.update(env)
     try:
@@ -182,3 +183,30 @@ def test_pr1_reference_output_ppm(renderer, cam, prec):
     d = np.abs(a - b)
     print(f"PR1 256x256 output.ppm, {prec}: bytes differing {int((d > 0).sum())} of {d.size}, max {int(d.max())}")
     assert d.max() <= 2 and (d > 1).sum() <= 3 and (d > 0).mean() < 0.02
+
+
+@pytest.mark.parametrize("prec", ["mixed", "fp16", "bf16"])
+def test_empty_sample_colour_skip_is_invisible(renderer, cam, prec):
+    """The fine pass does not evaluate the colour branch where a whole 256-sample slot has no density (a sample with
+    sigma = 0 has weight exactly 0 in integrate_ray, lib.rs:176-195): frames, depth and opacity must be bit-identical to
+    the pass that evaluates every colour, and a caller who asks for the rgb stage still gets every sample's colour."""
+    every = _fresh({"NERF_B200_SKIP_EMPTY": "0"})
+    try:
+        W, H = 160, 120
+        for kw in (dict(mode=nb.SAMPLING_DET), dict(mode=nb.SAMPLING_PHILOX, seed=12)):
+            a = every.render_image(cam, W, H, 64, 128, precision=prec, **kw)
+            b = renderer.render_image(cam, W, H, 64, 128, precision=prec, **kw)
+            assert (a == b).all() and np.isfinite(b).all()
+        assert 0.2 < float(np.all(b == 1.0, axis=1).mean()) < 0.95  # the frame has background to skip and an object not to
+        ra, da, aa = every.render_aux(cam, W, H, 64, 128, precision=prec)
+        rb, db, ab = renderer.render_aux(cam, W, H, 64, 128, precision=prec)
+        assert (ra == rb).all() and (da == db).all() and (aa == ab).all()
+        part = renderer.render_image(cam, W, H, 64, 128, precision=prec, ray_begin=777, ray_end=9999)
+        assert (part == renderer.render_image(cam, W, H, 64, 128, precision=prec)[777:9999]).all()
+        # the stage dump disables the skip: colours of empty samples are the network's, as in the other context
+        _, sa = every.render_image(cam, 48, 32, 64, 128, precision=prec, stages=True)
+        _, sb = renderer.render_image(cam, 48, 32, 64, 128, precision=prec, stages=True)
+        assert (sa["rgb_f"] == sb["rgb_f"]).all() and (sa["sigma_f"] == sb["sigma_f"]).all()
+        assert (sb["rgb_f"][sb["sigma_f"] == 0] > 0).all()  # sigmoid outputs, not the skip's zeros
+    finally:
+        every.close()
