@@ -178,6 +178,10 @@ def gpu_arm(args):
     rb, re_ = shard.ray_range(rank, world, n_rays)
     n_local = re_ - rb
     use_peer = world > 1 and args.gather == "peer"
+    # N > 1, default: the frame is dealt out in one-row stripes (stripe k -> rank k % N).  A ray's cost depends on what
+    # it hits (fewer refined coarse samples and no colour branch in empty rows), so contiguous ranges leave the ranks
+    # with the object 20 % behind; the NCCL-gather variant keeps contiguous ranges (it sends one block per rank).
+    striped = use_peer and not args.contiguous
     sf = None
     if use_peer:
         # the frame lives in rank 0's HBM; every rank maps it (VMM handle passed as a file descriptor) and its compositing
@@ -197,6 +201,10 @@ def gpu_arm(args):
             if sf is not None and rank == 0:
                 sf.close()
             sf, use_peer = None, False
+    if striped and sf is None:
+        striped = False
+    if striped:
+        n_local = len(shard.view_pixels(rank, world, W, n_rays))
     if use_peer:
         frame = sf.tensor() if rank == 0 else None
         mine = None
@@ -230,13 +238,20 @@ def gpu_arm(args):
             shard.gather_frame(mine, frame if rank == 0 else None, rank, world, dist)
 
     def step_device(prec=None):
-        r.render_device(cam, W, H, mine_ptr, NC, NF, precision=prec or args.precision, ray_begin=rb, ray_end=re_,
-                        stream=stream.cuda_stream)
+        if striped:
+            r.render_striped_device(cam, W, H, sf.row_ptr(0), W, world, rank, NC, NF, precision=prec or args.precision,
+                                    stream=stream.cuda_stream)
+        else:
+            r.render_device(cam, W, H, mine_ptr, NC, NF, precision=prec or args.precision, ray_begin=rb, ray_end=re_,
+                            stream=stream.cuda_stream)
         gather()
 
     def step_e2e():
         # nerf_render with host pointers: kernels + the D2H copy of this rank's rows, synchronous
-        r.render_image(cam, W, H, NC, NF, precision=args.precision, ray_begin=rb, ray_end=re_, out=host_frame[rb:re_])
+        if striped:
+            r.render_striped(cam, W, H, host_frame, W, world, rank, NC, NF, precision=args.precision)
+        else:
+            r.render_image(cam, W, H, NC, NF, precision=args.precision, ray_begin=rb, ray_end=re_, out=host_frame[rb:re_])
 
     def barrier():
         if world > 1:
@@ -357,7 +372,7 @@ def gpu_arm(args):
             "metric": "rays/s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "fp16" if args.precision == "mixed" else args.precision, "data": "synthetic",
-            "config": {"workload": WORKLOAD, "precision": PRECISION_NOTE.get(args.precision, args.precision), "parallelism": f"ray-range x{world}",
+            "config": {"workload": WORKLOAD, "precision": PRECISION_NOTE.get(args.precision, args.precision), "parallelism": (f"one-row stripes dealt to {world} ranks (stripe k -> rank k % {world})" if striped else f"ray-range x{world}"),
                        "l2": "flushed (256 MiB memset, untimed) before every step; per-frame intermediates ~3 GB >> 126 MB L2",
                        "timing": "value: per-rank CUDA events on the launching stream around the step (render + gather), every "
                                  "step started from a barrier, max over ranks; e2e: host wall clock from the same barrier to the "
@@ -511,6 +526,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                     help="N > 1: peer = compositing kernels store into rank 0's frame over NVLink; nccl = send/recv gather")
+    ap.add_argument("--contiguous", action="store_true",
+                    help="N > 1 with --gather peer: contiguous pixel-index ranges instead of interleaved one-row stripes")
     ap.add_argument("--orbit", type=int, default=0, help="run the multi-pose sweep with this many views instead")
     ap.add_argument("--res", type=int, default=1600, help="orbit sweep: frame width = height")
     args = ap.parse_args()

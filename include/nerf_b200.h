@@ -220,6 +220,19 @@ int nerf_sample_importance(nerf_ctx*, const float* t, const float* w, int64_t n_
 int nerf_integrate_rays(nerf_ctx*, const float* rgb, const float* sigma, const float* t, int64_t n_rays, int n,
                         float far_, float* out /*[n_rays][3]*/);             /* lib.rs:176-195 */
 
+/* Striped views: the frame's pixel indices are dealt out in stripes of `stripe_rays` to `parts` renderers in turn
+ * (stripe k of the frame belongs to part k % parts); this call renders part `part`.  The cost of a ray depends on what
+ * it hits - empty rows are cheaper than rows through the object since the mixed mode refines fewer coarse samples and
+ * the fine pass skips the colour of empty tiles there - so interleaved stripes, not contiguous ranges, are what balances
+ * several GPUs (rayon's work stealing over 8x8 blocks plays this role in the reference, lib.rs:533-550).  Pixels are
+ * bit-identical to the same pixels of a whole-frame render.  `d_frame` / `frame` is the WHOLE frame [W*H][3]; only the
+ * part's pixels are written.  Deterministic or Philox sampling. */
+int nerf_render_striped_device(nerf_ctx*, const nerf_camera*, int W, int H, int n_coarse, int n_fine, int precision,
+                               const nerf_sampling*, int64_t stripe_rays, int parts, int part, float* d_frame,
+                               void* stream);
+int nerf_render_striped(nerf_ctx*, const nerf_camera*, int W, int H, int n_coarse, int n_fine, int precision,
+                        const nerf_sampling*, int64_t stripe_rays, int parts, int part, float* frame);
+
 int nerf_get_timing(nerf_ctx*, nerf_timing* out);
 
 /* Host-side helpers of the boundary (no GPU needed). */

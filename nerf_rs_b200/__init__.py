@@ -34,7 +34,8 @@ EXPORTS = ["nerf_last_error", "nerf_version", "nerf_create", "nerf_create_from_t
            "nerf_save_ppm", "nerf_quantize_rgb8", "nerf_render_rgb8", "nerf_render_rgb8_device", "nerf_render_many",
            "nerf_quantize_rgb8_gpu", "nerf_render_aux", "nerf_render_aux_device", "nerf_build_weight_cache",
            "nerf_create_from_cache", "nerf_shared_frame_create", "nerf_shared_frame_open", "nerf_shared_frame_close",
-           "nerf_shared_frame_create_fd", "nerf_shared_frame_open_fd", "nerf_shared_frame_close_fd"]
+           "nerf_shared_frame_create_fd", "nerf_shared_frame_open_fd", "nerf_shared_frame_close_fd",
+           "nerf_render_striped", "nerf_render_striped_device"]
 
 
 E_ARG, E_IO, E_SHAPE, E_CUDA, E_UNSUPPORTED = -1, -2, -3, -4, -5  # nerf_status
@@ -109,6 +110,9 @@ def lib():
     L.nerf_render.argtypes = rargs + [_f32p]
     L.nerf_render_device.argtypes = rargs + [vp, vp]
     L.nerf_render_stages.argtypes = rargs + [_f32p, C.POINTER(Stages)]
+    sargs = rargs[:8] + [i64, i32, i32]
+    L.nerf_render_striped.argtypes = sargs + [_f32p]
+    L.nerf_render_striped_device.argtypes = sargs + [vp, vp]
     u8p = C.POINTER(C.c_uint8)
     L.nerf_render_rgb8.argtypes = rargs + [i32, u8p]
     L.nerf_render_rgb8_device.argtypes = rargs + [i32, vp, vp]

@@ -339,7 +339,11 @@ struct StagePtrs {  // device destinations for stage dumps (may be null)
 // MLP(fine) -> K4.  d_jit/d_u are device pointers indexed from ray rb.
 int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int nf, int precision, int mode,
                  uint64_t seed, const float* d_jit, const float* d_u, int64_t rb, int64_t re, float* d_rgb,
-                 bool want_wc, cudaStream_t s, float* d_depth = nullptr, float* d_acc = nullptr) {
+                 bool want_wc, cudaStream_t s, float* d_depth = nullptr, float* d_acc = nullptr,
+                 const RayMap* view = nullptr, bool compact_out = false) {
+  // view == nullptr: rays are the pixel indices [rb, re) and d_rgb / d_depth / d_acc point at pixel rb's element.
+  // view != nullptr: rays are the view's indices [rb, re) (RayMap::pixel names their pixels) and the outputs are
+  // whole-frame arrays indexed by pixel, or (compact_out) arrays indexed by view index.
   const RayBasis basis = make_basis(cam, W, H);
   const int nm = nc + nf;
   for (int64_t b0 = rb; b0 < re; b0 += c->chunk_rays) {
@@ -351,7 +355,9 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
         (want_wc && (rc = c->wc.reserve(n * nc * 4))))
       return rc;
     span_begin(c, ST_SAMPLING, s);
-    NERF_CUDA(launch_raygen_stratified(basis, nc, mode, seed, d_jit ? d_jit + off * nc : nullptr, b0, n,
+    const RayMap map = view ? RayMap{b0, view->stripe, view->parts, view->part} : RayMap{b0, 0, 1, 0};
+    const RayMap omap = (view && !compact_out) ? map : RayMap{off, 0, 1, 0};
+    NERF_CUDA(launch_raygen_stratified(basis, nc, mode, seed, d_jit ? d_jit + off * nc : nullptr, map, n,
                                        c->dirs.as<float>(), c->tc.as<float>(), s));
     span_end(c, s);
     ++c->launches;
@@ -396,7 +402,7 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
 
     span_begin(c, ST_SAMPLING, s);
     NERF_CUDA(launch_importance(c->tc.as<float>(), c->sigc.as<float>(), nullptr, nc, nf, cam.far_, mode, seed,
-                                d_u ? d_u + off * nf : nullptr, b0, n, c->tf.as<float>(),
+                                d_u ? d_u + off * nf : nullptr, map, n, c->tf.as<float>(),
                                 want_wc ? c->wc.as<float>() : nullptr, s));
     span_end(c, s);
     ++c->launches;
@@ -411,8 +417,8 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
     if (rc) return rc;
 
     span_begin(c, ST_COMPOSITE, s);
-    NERF_CUDA(launch_composite(c->rgbf.as<float>(), c->sigf.as<float>(), c->tf.as<float>(), n, nm, cam.far_,
-                               d_rgb + off * 3, d_depth ? d_depth + off : nullptr, d_acc ? d_acc + off : nullptr, s));
+    NERF_CUDA(launch_composite(c->rgbf.as<float>(), c->sigf.as<float>(), c->tf.as<float>(), n, nm, cam.far_, omap, d_rgb,
+                               d_depth, d_acc, s));
     span_end(c, s);
     ++c->launches;
   }
@@ -782,6 +788,85 @@ int nerf_render_stages(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc
   return render_host(c, cam, W, H, nc, nf, precision, smp, rb, re, rgb, st ? st : &none);
 }
 
+// ---------------------------------------------------------------------------- striped views (multi-GPU load balance)
+namespace nerf {
+namespace {
+int check_stripes(int W, int H, int64_t stripe, int parts, int part) {
+  if (stripe <= 0 || parts <= 0 || part < 0 || part >= parts || stripe > (int64_t)W * H) {
+    set_error("striped view: need stripe_rays > 0 and 0 <= part < parts");
+    return NERF_E_ARG;
+  }
+  return NERF_OK;
+}
+}  // namespace
+}  // namespace nerf
+
+int nerf_render_striped_device(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc, int nf, int precision,
+                               const nerf_sampling* smp, int64_t stripe_rays, int parts, int part, float* d_frame,
+                               void* stream) {
+  int rc = check_render_args(c, cam, W, H, nc, nf, smp, 0, (int64_t)W * H);
+  if (rc == NERF_OK) rc = check_stripes(W, H, stripe_rays, parts, part);
+  if (rc != NERF_OK) return rc;
+  if (smp && smp->mode == NERF_SAMPLING_ARRAYS) {
+    set_error("striped views take deterministic or Philox sampling (caller arrays are indexed by contiguous ranges)");
+    return NERF_E_UNSUPPORTED;
+  }
+  const int64_t n = view_size((int64_t)W * H, stripe_rays, parts, part);
+  if (n == 0) return NERF_OK;
+  if (!d_frame) {
+    set_error("nerf_render_striped: null output");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const RayMap view{0, stripe_rays, parts, part};
+  timing_start(c, s);
+  rc = render_range(c, *cam, W, H, nc, nf, precision, smp ? smp->mode : NERF_SAMPLING_DET, smp ? smp->seed : 0, nullptr,
+                    nullptr, 0, n, d_frame, false, s, nullptr, nullptr, &view);
+  timing_stop(c, s);
+  return rc;
+}
+
+int nerf_render_striped(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc, int nf, int precision,
+                        const nerf_sampling* smp, int64_t stripe_rays, int parts, int part, float* frame) {
+  int rc = check_render_args(c, cam, W, H, nc, nf, smp, 0, (int64_t)W * H);
+  if (rc == NERF_OK) rc = check_stripes(W, H, stripe_rays, parts, part);
+  if (rc != NERF_OK) return rc;
+  const int64_t total = (int64_t)W * H, n = view_size(total, stripe_rays, parts, part);
+  if (n == 0) return NERF_OK;
+  if (!frame) {
+    set_error("nerf_render_striped: null output");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);
+  // the view is rendered compactly (view index order) and its stripes are copied to their places in the caller's frame
+  if ((rc = c->out.reserve(n * 12))) return rc;
+  cudaStream_t s = c->stream;
+  {
+    // a compact view is a contiguous "frame" of its own for the compositing kernel: render with the view's pixel map
+    // for ray generation and Philox, but store by view index
+    const RayMap view{0, stripe_rays, parts, part};
+    timing_start(c, s);
+    rc = render_range(c, *cam, W, H, nc, nf, precision, smp ? smp->mode : NERF_SAMPLING_DET, smp ? smp->seed : 0, nullptr,
+                      nullptr, 0, n, c->out.as<float>(), false, s, nullptr, nullptr, &view, /*compact_out=*/true);
+    timing_stop(c, s);
+    if (rc != NERF_OK) return rc;
+  }
+  const size_t block = (size_t)stripe_rays * 12;
+  const int64_t full = n / stripe_rays, tail = n - full * stripe_rays;
+  if (full > 0)
+    NERF_CUDA(cudaMemcpy2DAsync(reinterpret_cast<char*>(frame) + (size_t)part * block, block * parts, c->out.p, block, block,
+                                (size_t)full, cudaMemcpyDeviceToHost, s));
+  if (tail > 0)
+    NERF_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(frame) + ((size_t)full * parts + part) * block,
+                              reinterpret_cast<const char*>(c->out.p) + (size_t)full * block, (size_t)tail * 12,
+                              cudaMemcpyDeviceToHost, s));
+  NERF_CUDA(cudaStreamSynchronize(s));
+  return NERF_OK;
+}
+
 // ---------------------------------------------------------------------------- 8-bit output
 namespace nerf {
 namespace {
@@ -1043,7 +1128,7 @@ int nerf_sample_importance(nerf_ctx* c, const float* t, const float* w, int64_t 
   NERF_CUDA(cudaMemcpyAsync(c->tc.p, t, n_rays * n * 4, cudaMemcpyHostToDevice, c->stream));
   if (count > 0) NERF_CUDA(cudaMemcpyAsync(c->uni.p, u, n_rays * count * 4, cudaMemcpyHostToDevice, c->stream));
   NERF_CUDA(launch_importance(c->tc.as<float>(), nullptr, c->wc.as<float>(), n, count, 0.0f, NERF_SAMPLING_ARRAYS, 0,
-                              c->uni.as<float>(), 0, n_rays, c->tf.as<float>(), nullptr, c->stream));
+                              c->uni.as<float>(), RayMap{0, 0, 1, 0}, n_rays, c->tf.as<float>(), nullptr, c->stream));
   NERF_CUDA(cudaMemcpyAsync(t_merged, c->tf.p, n_rays * nm * 4, cudaMemcpyDeviceToHost, c->stream));
   NERF_CUDA(cudaStreamSynchronize(c->stream));
   return NERF_OK;
@@ -1069,7 +1154,7 @@ int nerf_integrate_rays(nerf_ctx* c, const float* rgb, const float* sigma, const
     NERF_CUDA(cudaMemcpyAsync(c->tf.p, t, n_rays * n * 4, cudaMemcpyHostToDevice, c->stream));
   }
   NERF_CUDA(launch_composite(c->rgbf.as<float>(), c->sigf.as<float>(), c->tf.as<float>(), n_rays, n, far_,
-                             c->out.as<float>(), nullptr, nullptr, c->stream));
+                             RayMap{0, 0, 1, 0}, c->out.as<float>(), nullptr, nullptr, c->stream));
   NERF_CUDA(cudaMemcpyAsync(out, c->out.p, n_rays * 12, cudaMemcpyDeviceToHost, c->stream));
   NERF_CUDA(cudaStreamSynchronize(c->stream));
   return NERF_OK;

@@ -72,6 +72,28 @@ struct RayBasis {
   int nx, ny;
 };
 
+// Which pixel a launch's ray r is.  A contiguous range (parts <= 1): pixel = first + r.  A striped view - the share of
+// part `part` when the frame is dealt out in stripes of `stripe` pixel indices to `parts` renderers in turn, which
+// balances the data-dependent work (empty rows are cheaper than rows through the object) across GPUs: view index
+// q = first + r lies in the view's stripe q / stripe, which is the frame's stripe (q / stripe) * parts + part.
+struct RayMap {
+  int64_t first;
+  int64_t stripe;
+  int32_t parts, part;
+  __host__ __device__ int64_t pixel(int64_t r) const {
+    const int64_t q = first + r;
+    if (parts <= 1) return q;
+    const int64_t k = q / stripe;
+    return (k * parts + part) * stripe + (q - k * stripe);
+  }
+};
+// Number of pixels of a striped view of an n-pixel frame.
+inline int64_t view_size(int64_t n, int64_t stripe, int parts, int part) {
+  const int64_t round = stripe * parts, full = n / round, rest = n - full * round;
+  const int64_t tail = rest - (int64_t)part * stripe;
+  return full * stripe + (tail <= 0 ? 0 : (tail < stripe ? tail : stripe));
+}
+
 // ------------------------------------------------------------------ Philox4x32-10 (shared with oracle)
 __host__ __device__ inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
 #pragma unroll
@@ -100,12 +122,12 @@ cudaError_t launch_mlp_fp32(const NetF32& net, const SampleSrc& src, const Sampl
 // sampling.cu
 cudaError_t init_sampling();
 cudaError_t launch_raygen_stratified(const RayBasis& rb, int nc, int mode, uint64_t seed, const float* d_jitter,
-                                     int64_t ray_begin, int64_t n_rays, float* d_dirs, float* d_tc, cudaStream_t s);
+                                     RayMap map, int64_t n_rays, float* d_dirs, float* d_tc, cudaStream_t s);
 cudaError_t launch_ray_dirs(const RayBasis& rb, int64_t ray_begin, int64_t n_rays, float* d_dirs, cudaStream_t s);
 // weights come from d_sigc (compute_weights) unless d_w_in is given (stage entry point).
 cudaError_t launch_importance(const float* d_tc, const float* d_sigc, const float* d_w_in, int nc, int nf, float far_,
                               int mode,
-                              uint64_t seed, const float* d_u, int64_t ray_begin, int64_t n_rays, float* d_tf,
+                              uint64_t seed, const float* d_u, RayMap map, int64_t n_rays, float* d_tf,
                               float* d_wc_or_null, cudaStream_t s);
 // Two-pass coarse densities: d_sig holds the single-pass fp16 pre-activations on entry and
 // relu(pre-activation) on return; the ids of the samples whose density can reach the coarse weights are appended to
@@ -115,8 +137,9 @@ cudaError_t launch_coarse_select(float* d_sig, const float* d_t, int64_t n_rays,
 cudaError_t launch_weights(const float* d_sigma, const float* d_t, int64_t n_rays, int n, float far_, float* d_w,
                            cudaStream_t s);
 cudaError_t launch_quantize(const float* d_rgb, int64_t n_pixels, int channels, uint8_t* d_out, cudaStream_t s);
+// ray r's outputs go to element omap.pixel(r) of d_out / d_depth / d_acc
 cudaError_t launch_composite(const float* d_rgb, const float* d_sigma, const float* d_t, int64_t n_rays, int n,
-                             float far_, float* d_out, float* d_depth /*nullable*/, float* d_acc /*nullable*/,
+                             float far_, RayMap omap, float* d_out, float* d_depth /*nullable*/, float* d_acc /*nullable*/,
                              cudaStream_t s);
 
 }  // namespace nerf

@@ -6,9 +6,10 @@
 // output.ppm (save_ppm, lib.rs:567-580).  The flags only expose what the reference hard-codes.
 //
 // --gpus N spreads the frame over N devices the way the reference spreads it over cores (rayon par_iter over pixel
-// blocks, lib.rs:533-550): one context and one host thread per GPU, each rendering a contiguous pixel-index range
-// straight into its rows of the host frame; every ray costs the same, so equal ranges are balanced.  --cache FILE
-// starts from the pre-swizzled weight cache (written on first use).
+// blocks, lib.rs:533-550): one context and one host thread per GPU, each rendering its share of the frame straight
+// into the host frame.  The shares are interleaved one-row stripes (row k -> GPU k % N), not contiguous ranges: rows
+// through empty space are cheaper than rows through the object, and rayon's work stealing balances the same thing in
+// the reference.  --cache FILE starts from the pre-swizzled weight cache (written on first use).
 //
 // The reference jitters samples with an OS-seeded thread_rng (lib.rs:375,407); the default here is the seeded
 // Philox stream (--seed), --det selects the deterministic mid-point sampling used by the parity tests.
@@ -112,8 +113,8 @@ int main(int argc, char** argv) {
     std::vector<std::thread> workers;
     for (int g = 0; g < gpus; ++g) {
       workers.emplace_back([&, g] {
-        const int64_t rb = g * n_rays / gpus, re = (g + 1) * n_rays / gpus;
-        status[g] = nerf_render(ctx[g], &cam, W, H, nc, nf, precision, &smp, rb, re, rgb.data() + 3 * rb);
+        status[g] = gpus == 1 ? nerf_render(ctx[g], &cam, W, H, nc, nf, precision, &smp, 0, n_rays, rgb.data())
+                              : nerf_render_striped(ctx[g], &cam, W, H, nc, nf, precision, &smp, W, gpus, g, rgb.data());
         if (status[g] != NERF_OK) errors[g] = nerf_last_error();  // the message is thread-local
       });
     }

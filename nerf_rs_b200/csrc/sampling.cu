@@ -35,14 +35,14 @@ __device__ __forceinline__ void ray_dir_normalized(const RayBasis& rb, int64_t p
 // K1: one thread per (ray, coarse sample); thread s==0 of a ray also writes the direction.
 __global__ void __launch_bounds__(256) raygen_stratified_kernel(RayBasis rb, int nc, int mode, uint64_t seed,
                                                                const float* __restrict__ jitter,
-                                                               int64_t ray_begin, int64_t n_rays,
+                                                               RayMap map, int64_t n_rays,
                                                                float* __restrict__ dirs, float* __restrict__ tc) {
   const int64_t total = n_rays * nc;
   const float interval = (rb.far_ - rb.near_) / (float)nc;  // lib.rs:239
   for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
     const int64_t ray = e / nc;
     const int s = (int)(e - ray * nc);
-    const int64_t pixel = ray_begin + ray;
+    const int64_t pixel = map.pixel(ray);
     float jit;
     if (mode == NERF_SAMPLING_DET) jit = 0.5f;
     else if (mode == NERF_SAMPLING_PHILOX) jit = philox_uniform(seed, (uint32_t)pixel, 0u, s);
@@ -151,7 +151,7 @@ __device__ __forceinline__ int count_less(const float* a, int n, float v, bool o
 __global__ void __launch_bounds__(kWarpsPerCta * 32) importance_kernel(
     const float* __restrict__ tc, const float* __restrict__ sigc, const float* __restrict__ w_in, int nc, int nf,
     float far_, int mode, uint64_t seed,
-    const float* __restrict__ u_in, int64_t ray_begin, int64_t n_rays, float* __restrict__ tf,
+    const float* __restrict__ u_in, RayMap map, int64_t n_rays, float* __restrict__ tf,
     float* __restrict__ wc_out) {
   extern __shared__ float smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) importance_kernel(
       __syncwarp();
       if (lane == 0) s_cdf[m] = 1.0f;  // lib.rs:327
       __syncwarp();
-      const int64_t pixel = ray_begin + ray;
+      const int64_t pixel = map.pixel(ray);
       if (mode == NERF_SAMPLING_PHILOX) {
         // one Philox4x32-10 block yields four consecutive uniforms (philox_uniform: block k / 4, element k % 4): evaluate
         // each block once and park the uniforms in s_f, which the loop below overwrites element by element
@@ -388,7 +388,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) weights_kernel(const float*
 __global__ void __launch_bounds__(kWarpsPerCta * 32) composite_kernel(const float* __restrict__ rgb,
                                                                       const float* __restrict__ sigma,
                                                                       const float* __restrict__ t, int64_t n_rays,
-                                                                      int n, float far_, float* __restrict__ out,
+                                                                      int n, float far_, RayMap omap,
+                                                                      float* __restrict__ out,
                                                                       float* __restrict__ depth_out,
                                                                       float* __restrict__ acc_out) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -422,12 +423,13 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) composite_kernel(const floa
       depth += __shfl_xor_sync(kFull, depth, d);
     }
     // optional outputs the reference does not have: depth = sum w_i t_i, accumulated opacity = sum w_i
-    if (lane == 0 && depth_out != nullptr) depth_out[ray] = depth;
-    if (lane == 0 && acc_out != nullptr) acc_out[ray] = acc;
+    const int64_t opix = omap.pixel(ray);
+    if (lane == 0 && depth_out != nullptr) depth_out[opix] = depth;
+    if (lane == 0 && acc_out != nullptr) acc_out[opix] = acc;
     if (n == 0) { r = g = b = 0.0f; acc = 1.0f; }  // lib.rs:178-180: no samples -> black
     const float bg = 1.0f - acc;                   // lib.rs:194
     const float v = lane == 0 ? r + bg : (lane == 1 ? g + bg : b + bg);
-    if (lane < 3) out[ray * 3 + lane] = v;  // one 12-byte coalesced store per ray
+    if (lane < 3) out[opix * 3 + lane] = v;  // one 12-byte coalesced store per ray
   }
 }
 
@@ -451,9 +453,9 @@ cudaError_t init_sampling() {  // once per device, at context creation
 }
 
 cudaError_t launch_raygen_stratified(const RayBasis& rb, int nc, int mode, uint64_t seed, const float* d_jitter,
-                                     int64_t ray_begin, int64_t n_rays, float* d_dirs, float* d_tc, cudaStream_t s) {
+                                     RayMap map, int64_t n_rays, float* d_dirs, float* d_tc, cudaStream_t s) {
   if (n_rays == 0) return cudaSuccess;
-  raygen_stratified_kernel<<<grid_for(n_rays * nc, 256), 256, 0, s>>>(rb, nc, mode, seed, d_jitter, ray_begin, n_rays,
+  raygen_stratified_kernel<<<grid_for(n_rays * nc, 256), 256, 0, s>>>(rb, nc, mode, seed, d_jitter, map, n_rays,
                                                                        d_dirs, d_tc);
   return cudaGetLastError();
 }
@@ -465,13 +467,13 @@ cudaError_t launch_ray_dirs(const RayBasis& rb, int64_t ray_begin, int64_t n_ray
 }
 
 cudaError_t launch_importance(const float* d_tc, const float* d_sigc, const float* d_w_in, int nc, int nf, float far_,
-                              int mode, uint64_t seed, const float* d_u, int64_t ray_begin, int64_t n_rays, float* d_tf,
+                              int mode, uint64_t seed, const float* d_u, RayMap map, int64_t n_rays, float* d_tf,
                               float* d_wc, cudaStream_t s) {
   if (n_rays == 0) return cudaSuccess;
   const size_t smem = importance_smem_bytes(nc, nf);
   if (smem > kImportanceMaxSmem) return cudaErrorInvalidValue;
   importance_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, smem, s>>>(
-      d_tc, d_sigc, d_w_in, nc, nf, far_, mode, seed, d_u, ray_begin, n_rays, d_tf, d_wc);
+      d_tc, d_sigc, d_w_in, nc, nf, far_, mode, seed, d_u, map, n_rays, d_tf, d_wc);
   return cudaGetLastError();
 }
 
@@ -517,10 +519,10 @@ cudaError_t launch_quantize(const float* d_rgb, int64_t n_pixels, int channels, 
 }
 
 cudaError_t launch_composite(const float* d_rgb, const float* d_sigma, const float* d_t, int64_t n_rays, int n,
-                             float far_, float* d_out, float* d_depth, float* d_acc, cudaStream_t s) {
+                             float far_, RayMap omap, float* d_out, float* d_depth, float* d_acc, cudaStream_t s) {
   if (n_rays == 0) return cudaSuccess;
   composite_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, 0, s>>>(d_rgb, d_sigma, d_t, n_rays, n, far_,
-                                                                                d_out, d_depth, d_acc);
+                                                                                omap, d_out, d_depth, d_acc);
   return cudaGetLastError();
 }
 

@@ -136,6 +136,23 @@ class Renderer:
         _check(lib().nerf_render_device(self._h, C.byref(cam), W, H, n_coarse, n_fine, _prec(precision), C.byref(smp),
                                         ray_begin, ray_end, d_rgb, stream))
 
+    def render_striped(self, cam, W, H, frame, stripe_rays, parts, part, n_coarse=64, n_fine=128, precision="mixed",
+                       mode=SAMPLING_DET, seed=0):
+        """Renders part `part` of the frame dealt out in stripes of `stripe_rays` pixel indices to `parts` renderers
+        (stripe k belongs to part k % parts) into the whole-frame host array `frame` [W*H, 3]; other pixels are left."""
+        assert frame.dtype == np.float32 and frame.size == W * H * 3 and frame.flags["C_CONTIGUOUS"]
+        smp = Sampling(mode=mode, seed=seed)
+        _check(lib().nerf_render_striped(self._h, C.byref(cam), W, H, n_coarse, n_fine, _prec(precision), C.byref(smp),
+                                         stripe_rays, parts, part, _p(frame)))
+        return frame
+
+    def render_striped_device(self, cam, W, H, d_frame, stripe_rays, parts, part, n_coarse=64, n_fine=128,
+                              precision="mixed", mode=SAMPLING_DET, seed=0, stream=0):
+        """The same into a whole-frame device buffer (int pointer), enqueued on `stream`."""
+        smp = Sampling(mode=mode, seed=seed)
+        _check(lib().nerf_render_striped_device(self._h, C.byref(cam), W, H, n_coarse, n_fine, _prec(precision),
+                                                C.byref(smp), stripe_rays, parts, part, d_frame, stream))
+
     # ------------------------------------------------------------------ 8-bit output (save_ppm / pixels_to_rgba, lib.rs:567-592)
     def render_rgb8(self, cam, W, H, n_coarse=64, n_fine=128, precision="mixed", mode=SAMPLING_DET, seed=0,
                     jitter=None, u=None, ray_begin=0, ray_end=None, channels=3):

@@ -17,6 +17,21 @@ def ray_counts(world, n_rays):
     return [ray_range(r, world, n_rays)[1] - ray_range(r, world, n_rays)[0] for r in range(world)]
 
 
+def view_pixels(part, parts, stripe, n_rays):
+    """Pixel indices of part `part` when the frame's n_rays pixel indices are dealt out in stripes of `stripe` to
+    `parts` renderers in turn (stripe k belongs to part k % parts) - the numpy statement of RayMap::pixel /
+    view_size (csrc/common.cuh), in view order.  Interleaved stripes balance the data-dependent cost of rays (empty
+    rows are cheaper than rows through the object) that contiguous ranges do not."""
+    import numpy as np
+    if not 0 <= part < parts or stripe <= 0:
+        raise ValueError("need stripe > 0 and 0 <= part < parts")
+    starts = np.arange(part * stripe, n_rays, stripe * parts, dtype=np.int64)
+    if len(starts) == 0:
+        return np.zeros(0, np.int64)
+    idx = (starts[:, None] + np.arange(stripe, dtype=np.int64)[None, :]).ravel()
+    return idx[idx < n_rays]
+
+
 def gather_frame(local, frame, rank, world, dist=None, group=None):
     """Gathers each rank's [n_local, 3] rgb rows into `frame` [n_rays, 3] on rank 0 (NCCL over NVLink on GPUs,
     gloo in the CPU tests).  `frame` is only read on rank 0; with world == 1 it must alias `local`."""

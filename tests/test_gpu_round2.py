@@ -210,3 +210,31 @@ def test_empty_sample_colour_skip_is_invisible(renderer, cam, prec):
         assert (sb["rgb_f"][sb["sigma_f"] == 0] > 0).all()  # sigmoid outputs, not the skip's zeros
     finally:
         every.close()
+
+
+def test_striped_views_assemble_the_frame_bit_for_bit(renderer, cam):
+    """nerf_render_striped(_device): the frame dealt out in stripes to N renderers and rendered part by part equals the
+    whole-frame render bit for bit - host frame and device frame, deterministic and Philox sampling, stripes that do
+    not divide the frame - and each part only touches its own pixels."""
+    import torch
+    from nerf_rs_b200 import shard
+    W, H = 64, 40
+    n = W * H
+    for kw in (dict(mode=nb.SAMPLING_DET), dict(mode=nb.SAMPLING_PHILOX, seed=21)):
+        want = renderer.render_image(cam, W, H, 64, 128, precision="mixed", **kw)
+        for stripe, parts in ((W, 4), (3 * W + 5, 3), (n, 2), (17, 5)):
+            host = np.full((n, 3), -7.0, np.float32)
+            dev = torch.full((n, 3), -7.0, device="cuda:0")
+            for part in range(parts):
+                before = host.copy()
+                renderer.render_striped(cam, W, H, host, stripe, parts, part, precision="mixed", **kw)
+                renderer.render_striped_device(cam, W, H, dev.data_ptr(), stripe, parts, part, precision="mixed", **kw)
+                mine = shard.view_pixels(part, parts, stripe, n)
+                other = np.setdiff1d(np.arange(n), mine)
+                assert (host[other] == before[other]).all() and (host[mine] == want[mine]).all(), (stripe, parts, part)
+            torch.cuda.synchronize()
+            assert (host == want).all() and (dev.cpu().numpy() == want).all(), (stripe, parts)
+    with pytest.raises(nb.NerfError):
+        renderer.render_striped(cam, W, H, np.zeros((n, 3), np.float32), 0, 2, 0)
+    with pytest.raises(nb.NerfError):
+        renderer.render_striped(cam, W, H, np.zeros((n, 3), np.float32), W, 2, 2)

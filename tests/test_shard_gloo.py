@@ -63,3 +63,20 @@ def test_gather_equals_single_rank(tmp_path, onets, ocam, world):
     mp.spawn(_worker, args=(world, _free_port(), out), nprocs=world, join=True)
     want = O.render(onets[0], onets[1], ocam, W, H, NC, NF)
     assert (np.load(out) == want).all()  # bit for bit: a ray range renders exactly the rows of the full frame
+
+
+def test_striped_views_partition_the_frame():
+    """Every pixel belongs to exactly one part, in ascending order inside a part, for ragged sizes too."""
+    import numpy as np
+    from nerf_rs_b200 import shard
+    for n, stripe, parts in ((640000, 800, 8), (640000, 800, 3), (1000, 64, 4), (10, 64, 4), (7, 1, 3), (129, 128, 2)):
+        views = [shard.view_pixels(p, parts, stripe, n) for p in range(parts)]
+        for v in views:
+            assert (np.diff(v) > 0).all()
+        allpix = np.sort(np.concatenate(views))
+        assert (allpix == np.arange(n)).all()
+        sizes = [len(v) for v in views]
+        assert max(sizes) - min(sizes) <= stripe
+    import pytest
+    with pytest.raises(ValueError):
+        shard.view_pixels(2, 2, 8, 100)
