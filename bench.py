@@ -496,6 +496,22 @@ def orbit_arm(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     clk = clocks.stop() if clocks else {}
     checksum = int(frames.astype(np.uint64).sum()) if len(mine) else 0
+    parity = None
+    if rank == 0 and len(mine) and not args.no_cpu:
+        # pose 0, eight rows through the middle of the frame: the CPU oracle at this resolution against the 8-bit frame
+        from oracle import pyoracle as O
+        p0 = nb.orbit_poses(os.path.join(nb.DATA_ROOT, "tf_reference_samples.json"), args.orbit)[0]
+        ocam = O.camera_from_values(p0["near"], p0["far"], p0["camera_origin"], p0["camera_forward"], p0["camera_up"], p0["hwf"])
+        oc, of = O.Network(nb.DATA_ROOT + "/coarse"), O.Network(nb.DATA_ROOT + "/fine")
+        begin = (R // 2) * R
+        band = O.render(oc, of, ocam, R, R, NC, NF, ray_begin=begin, ray_end=begin + 8 * R,
+                        threads=len(os.sched_getaffinity(0)))
+        want = O.quantize(band).reshape(-1, 3).astype(np.int16)
+        got = frames[0][begin:begin + 8 * R].astype(np.int16)
+        d = np.abs(got - want).max(axis=1)
+        parity = {"vs": "CPU oracle, pose 0, rows %d..%d of the %dx%d frame, 8-bit values" % (R // 2, R // 2 + 7, R, R),
+                  "rays": int(d.size), "max_abs_diff_of_255": int(d.max()), "pixels_over_2_255": int((d > 2).sum()),
+                  "psnr_db": float(10 * np.log10(255.0 ** 2 / max(float(np.mean((got - want).astype(np.float64) ** 2)), 1e-12)))}
     if rank == 0:
         dt = float(t.item())
         n_rays = args.orbit * R * R
@@ -509,7 +525,7 @@ def orbit_arm(args):
                        "parallelism": f"views x{world} ({ve - vb} views on rank 0)"},
             "samples_per_s": n_rays / dt * (NC + NC + NF), "views_per_s": args.orbit / dt,
             "tflops": n_rays * (NC * FLOP_COARSE + (NC + NF) * FLOP_FINE) / dt / 1e12,
-            "d2h_bytes": n_rays * 3, "clocks": clk, "rank0_checksum": checksum}))
+            "d2h_bytes": n_rays * 3, "clocks": clk, "rank0_checksum": checksum, "parity": parity}))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
