@@ -621,6 +621,19 @@ void nerf_destroy(nerf_ctx* c) {
   {
     DeviceGuard g(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (!c->vmm_frames.empty()) {  // shared frames the caller never closed: unmap and drop this context's references
+      cudaDeviceSynchronize();
+      const VmmApi& a = vmm_api();
+      for (auto& kv : c->vmm_frames) {
+        const CUdeviceptr va = reinterpret_cast<CUdeviceptr>(kv.first);
+        if (a.ok) {
+          a.unmap(va, kv.second.size);
+          a.addr_free(va, kv.second.size);
+          a.release(kv.second.handle);
+        }
+      }
+      c->vmm_frames.clear();
+    }
     for (DevBuf* b : {&c->dirs, &c->tc, &c->sigc, &c->wc, &c->tf, &c->sigf, &c->rgbf, &c->out, &c->in_a, &c->in_b,
                       &c->jit, &c->uni, &c->q8[0], &c->q8[1], &c->depth, &c->acc, &c->sel_list, &c->sel_count})
       b->release();

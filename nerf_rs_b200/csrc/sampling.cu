@@ -388,15 +388,28 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) weights_kernel(const float*
 __global__ void __launch_bounds__(kWarpsPerCta * 32) composite_kernel(const float* __restrict__ rgb,
                                                                       const float* __restrict__ sigma,
                                                                       const float* __restrict__ t, int64_t n_rays,
-                                                                      int n, float far_, RayMap omap,
+                                                                      int n, float far_, RayMap omap, bool staged,
                                                                       float* __restrict__ out,
                                                                       float* __restrict__ depth_out,
                                                                       float* __restrict__ acc_out) {
+  extern __shared__ float4 s_stage[];  // staged launches: one ray's colours per warp, [n * 3] floats
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // A ray's colours are n * 3 consecutive floats; read lane by lane that is three 4-byte loads at a 12-byte stride.
+  // When the block is 16-byte aligned (n * 3 a multiple of 4) the warp copies it with 128-bit loads into shared
+  // memory first and picks its samples from there (stride 3 words: no bank conflicts).
+  const float* s_rgb = reinterpret_cast<const float*>(s_stage) + (size_t)warp * n * 3;
   for (int64_t ray = blockIdx.x * (int64_t)kWarpsPerCta + warp; ray < n_rays; ray += (int64_t)gridDim.x * kWarpsPerCta) {
     const float* sr = sigma + ray * n;
     const float* tr = t + ray * n;
     const float* cr = rgb + ray * n * 3;
+    if (staged) {
+      __syncwarp();  // the previous ray's reads are done
+      const float4* src4 = reinterpret_cast<const float4*>(cr);
+      float4* dst4 = s_stage + (size_t)warp * (n * 3 / 4);
+      for (int k = lane; k < n * 3 / 4; k += 32) dst4[k] = __ldg(src4 + k);
+      __syncwarp();
+      cr = s_rgb;
+    }
     float r = 0.0f, g = 0.0f, b = 0.0f, acc = 0.0f, depth = 0.0f, carry = 1.0f;
     for (int base = 0; base < n; base += 32) {
       const int i = base + lane;
@@ -521,8 +534,10 @@ cudaError_t launch_quantize(const float* d_rgb, int64_t n_pixels, int channels, 
 cudaError_t launch_composite(const float* d_rgb, const float* d_sigma, const float* d_t, int64_t n_rays, int n,
                              float far_, RayMap omap, float* d_out, float* d_depth, float* d_acc, cudaStream_t s) {
   if (n_rays == 0) return cudaSuccess;
-  composite_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, 0, s>>>(d_rgb, d_sigma, d_t, n_rays, n, far_,
-                                                                                omap, d_out, d_depth, d_acc);
+  const size_t stage = (size_t)kWarpsPerCta * n * 3 * sizeof(float);
+  const bool staged = n > 0 && (n * 3) % 4 == 0 && stage <= 48 * 1024 && (reinterpret_cast<uintptr_t>(d_rgb) & 15u) == 0;
+  composite_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, staged ? stage : 0, s>>>(
+      d_rgb, d_sigma, d_t, n_rays, n, far_, omap, staged, d_out, d_depth, d_acc);
   return cudaGetLastError();
 }
 
