@@ -233,6 +233,21 @@ int nerf_render_striped_device(nerf_ctx*, const nerf_camera*, int W, int H, int 
 int nerf_render_striped(nerf_ctx*, const nerf_camera*, int W, int H, int n_coarse, int n_fine, int precision,
                         const nerf_sampling*, int64_t stripe_rays, int parts, int part, float* frame);
 
+/* No counterpart in the reference: added for callers that may not allocate
+ * device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * nerf_integrate_rays with its device scratch (the staged rgb / sigma / t inputs and the output) in ONE file-scope static
+ * device array instead of cudaMalloc'ed workspaces: the call performs no cudaMalloc, no cudaFree and calls no allocating
+ * library routine.  Same arguments (host pointers), same kernel, same result as nerf_integrate_rays.
+ *   - Limit: the four segments, each rounded up to 256 B - 12*n_rays*n + 4*n_rays*n + 4*n_rays*n + 12*n_rays bytes -
+ *     must fit NERF_NOALLOC_MAX_BYTES (1 088 rays per call at 64 + 128 samples per ray).  A larger call is refused with
+ *     NERF_E_UNSUPPORTED and a message naming the sizes; nothing is truncated.
+ *   - Every GPU that loads the library holds the array until the process exits.
+ *   - Every call on a device shares the array and finds the last call's contents in it; each call overwrites what it
+ *     reads, so nothing needs clearing.  Calls that overlap on the GPU (two contexts on one device) race: serialise them. */
+#define NERF_NOALLOC_MAX_BYTES (4u << 20)
+int nerf_integrate_rays_noalloc(nerf_ctx*, const float* rgb, const float* sigma, const float* t, int64_t n_rays, int n,
+                                float far_, float* out /*[n_rays][3]*/);
+
 int nerf_get_timing(nerf_ctx*, nerf_timing* out);
 
 /* Host-side helpers of the boundary (no GPU needed). */

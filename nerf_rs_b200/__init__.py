@@ -35,7 +35,8 @@ EXPORTS = ["nerf_last_error", "nerf_version", "nerf_create", "nerf_create_from_t
            "nerf_quantize_rgb8_gpu", "nerf_render_aux", "nerf_render_aux_device", "nerf_build_weight_cache",
            "nerf_create_from_cache", "nerf_shared_frame_create", "nerf_shared_frame_open", "nerf_shared_frame_close",
            "nerf_shared_frame_create_fd", "nerf_shared_frame_open_fd", "nerf_shared_frame_close_fd",
-           "nerf_render_striped", "nerf_render_striped_device"]
+           "nerf_render_striped", "nerf_render_striped_device", "nerf_integrate_rays_noalloc"]
+NOALLOC_MAX_BYTES = 4 << 20  # NERF_NOALLOC_MAX_BYTES (include/nerf_b200.h)
 
 
 E_ARG, E_IO, E_SHAPE, E_CUDA, E_UNSUPPORTED = -1, -2, -3, -4, -5  # nerf_status
@@ -124,6 +125,7 @@ def lib():
     L.nerf_compute_weights.argtypes = [vp, _f32p, _f32p, i64, i32, C.c_float, _f32p]
     L.nerf_sample_importance.argtypes = [vp, _f32p, _f32p, i64, i32, _f32p, i32, _f32p]
     L.nerf_integrate_rays.argtypes = [vp, _f32p, _f32p, _f32p, i64, i32, C.c_float, _f32p]
+    L.nerf_integrate_rays_noalloc.argtypes = [vp, _f32p, _f32p, _f32p, i64, i32, C.c_float, _f32p]
     L.nerf_get_timing.argtypes = [vp, C.POINTER(Timing)]
     L.nerf_camera_from_json.argtypes = [C.c_char_p, C.POINTER(Camera)]
     d3 = C.POINTER(C.c_double)

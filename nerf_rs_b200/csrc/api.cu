@@ -1334,3 +1334,103 @@ int nerf_get_timing(nerf_ctx* c, nerf_timing* out) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------- allocation-free compositing
+// nerf_integrate_rays_noalloc: integrate_ray (lib.rs:176-195) for callers that may not allocate device memory (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  nerf_integrate_rays stages its
+// host inputs and its output in four cudaMalloc'ed workspaces (DevBuf::reserve); here the same compositing kernel gets
+// that scratch from ONE file-scope device array of fixed size, so the call performs no cudaMalloc / cudaFree and calls
+// no allocating library routine; the reference has no counterpart.
+//
+//   - Limit: the staged inputs + output of a call must fit NERF_NOALLOC_MAX_BYTES (4 MiB; each of the four segments is
+//     rounded up to 256 B).  At the reference's 64 + 128 samples per ray that is 1 088 rays per call.  Larger calls are
+//     refused with NERF_E_UNSUPPORTED and a message that names the sizes - they are never truncated.
+//   - The array lives in every GPU that loads the library, from load to exit, whether the entry point is used or not.
+//   - Every call on a device shares the array and finds the previous call's contents in it.  Nothing has to start at
+//     zero: the three input segments are overwritten by this call's host-to-device copies before the kernel reads them,
+//     and the kernel writes all 3 floats of every ray of the output segment before it is copied back; bytes beyond this
+//     call's sizes are never read.  Calls that overlap on the GPU (two contexts, or two processes' worth of streams, on
+//     one device) RACE on the array: serialise them.  Calls on one context cannot overlap - the call holds the context's
+//     mutex and returns only after its stream has drained.
+//   - `g_noalloc_scratch` below is, in host code, a host-side stand-in for the symbol, NOT a device address: handing it
+//     to a kernel faults (or, where the GPU can reach host memory, silently uses the wrong memory).  The device address
+//     is fetched once per device with cudaGetSymbolAddress, with that device current, and that is what the kernel gets.
+namespace nerf {
+namespace {
+
+constexpr size_t kNoAllocMaxBytes = NERF_NOALLOC_MAX_BYTES;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocMaxBytes];
+
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_ptr[kNoAllocMaxDevices] = {};  // device address of g_noalloc_scratch, per device ordinal
+
+// Device address of the scratch array on `device`, which must be the current device.
+int noalloc_scratch(int device, unsigned char** out) {
+  if (device < 0 || device >= kNoAllocMaxDevices) {
+    set_error("nerf_integrate_rays_noalloc: device ordinal beyond the scratch table");
+    return NERF_E_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (g_noalloc_ptr[device] == nullptr) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      set_error(std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e));
+      return NERF_E_CUDA;
+    }
+    g_noalloc_ptr[device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_noalloc_ptr[device];
+  return NERF_OK;
+}
+
+inline size_t round256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+}  // namespace
+}  // namespace nerf
+
+int nerf_integrate_rays_noalloc(nerf_ctx* c, const float* rgb, const float* sigma, const float* t, int64_t n_rays, int n,
+                                float far_, float* out) {
+  if (!c || n_rays < 0 || n < 0 || ((!rgb || !sigma || !t) && n_rays * n > 0) || (!out && n_rays > 0)) {
+    set_error("nerf_integrate_rays_noalloc: bad argument");
+    return NERF_E_ARG;
+  }
+  if (n_rays == 0) return NERF_OK;
+  // sizes first, in 64-bit arithmetic that cannot wrap: n_rays and n are bounded before they are multiplied
+  if ((uint64_t)n_rays > kNoAllocMaxBytes || (uint64_t)n > kNoAllocMaxBytes) {
+    set_error("nerf_integrate_rays_noalloc: request exceeds NERF_NOALLOC_MAX_BYTES (" + std::to_string(kNoAllocMaxBytes) +
+              " B of static device scratch); use nerf_integrate_rays");
+    return NERF_E_UNSUPPORTED;
+  }
+  const size_t samples = (size_t)n_rays * (size_t)n;
+  const size_t b_rgb = round256(samples * 12), b_sig = round256(samples * 4), b_t = round256(samples * 4),
+               b_out = round256((size_t)n_rays * 12);
+  const size_t need = b_rgb + b_sig + b_t + b_out;
+  if (need > kNoAllocMaxBytes) {
+    set_error("nerf_integrate_rays_noalloc: " + std::to_string(n_rays) + " rays x " + std::to_string(n) + " samples need " +
+              std::to_string(need) + " B of scratch, the static array holds NERF_NOALLOC_MAX_BYTES = " +
+              std::to_string(kNoAllocMaxBytes) + " B; split the call or use nerf_integrate_rays");
+    return NERF_E_UNSUPPORTED;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  DeviceGuard g(c->device);  // the symbol's address is per device: resolve it with the context's device current
+  unsigned char* base = nullptr;
+  int rc = noalloc_scratch(c->device, &base);
+  if (rc != NERF_OK) return rc;
+  float* d_rgb = reinterpret_cast<float*>(base);
+  float* d_sig = reinterpret_cast<float*>(base + b_rgb);
+  float* d_t = reinterpret_cast<float*>(base + b_rgb + b_sig);
+  float* d_out = reinterpret_cast<float*>(base + b_rgb + b_sig + b_t);
+  cudaStream_t s = c->stream;
+  if (c->busy_recorded) NERF_CUDA(cudaStreamWaitEvent(s, c->ev_busy, 0));  // order after a *_device call on another stream
+  if (n > 0) {
+    NERF_CUDA(cudaMemcpyAsync(d_rgb, rgb, samples * 12, cudaMemcpyHostToDevice, s));
+    NERF_CUDA(cudaMemcpyAsync(d_sig, sigma, samples * 4, cudaMemcpyHostToDevice, s));
+    NERF_CUDA(cudaMemcpyAsync(d_t, t, samples * 4, cudaMemcpyHostToDevice, s));
+  }
+  NERF_CUDA(launch_composite(d_rgb, d_sig, d_t, n_rays, n, far_, RayMap{0, 0, 1, 0}, d_out, nullptr, nullptr, s));
+  NERF_CUDA(cudaMemcpyAsync(out, d_out, (size_t)n_rays * 12, cudaMemcpyDeviceToHost, s));
+  NERF_CUDA(cudaStreamSynchronize(s));
+  return NERF_OK;
+}
