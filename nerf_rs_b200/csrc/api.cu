@@ -81,7 +81,8 @@ struct nerf_ctx {
   DeviceNet nets[2];
   DevBuf dirs, tc, sigc, wc, tf, sigf, rgbf, out, in_a, in_b, jit, uni;
   // two-pass coarse densities of the mixed mode: ids of the samples the split-operand kernel re-evaluates
-  DevBuf sel_list, sel_count;
+  DevBuf sel_list, sel_count, alive[2];
+  int coarse_stages = 4;        // NERF_B200_COARSE_STAGES: slices of the front-to-back fp16 coarse pass (1 = one launch)
   bool coarse_select = true;    // NERF_B200_COARSE_SELECT=0: split-operand kernel over every coarse sample
   bool skip_empty = true;       // NERF_B200_SKIP_EMPTY=0: the fine pass evaluates the colour of empty samples too
   // NERF_B200_SELECT_MARGIN: bound on the fp16 pass's pre-activation error near zero.  Measured (scripts/select_check.py,
@@ -204,6 +205,7 @@ int create_common(const TensorMap& coarse, const TensorMap& fine, int device, ne
   }
   if (const char* e = std::getenv("NERF_B200_COARSE_SELECT")) ctx->coarse_select = std::atoi(e) != 0;
   if (const char* e = std::getenv("NERF_B200_SKIP_EMPTY")) ctx->skip_empty = std::atoi(e) != 0;
+  if (const char* e = std::getenv("NERF_B200_COARSE_STAGES")) ctx->coarse_stages = std::max(1, std::atoi(e));
   if (const char* e = std::getenv("NERF_B200_SELECT_MARGIN")) ctx->select_margin = (float)std::atof(e);
   if (const char* e = std::getenv("NERF_B200_SELECT_TAU")) ctx->select_tau = (float)std::atof(e);
   cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
@@ -376,7 +378,36 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
       if ((rc = c->sel_list.reserve(n * nc * 4)) || (rc = c->sel_count.reserve(256))) return rc;
       span_begin(c, ST_MLP_COARSE, s);
       dst.sigma_floor = -INFINITY;
-      rc = run_mlp(c, NERF_NET_COARSE, src, dst, NERF_PREC_FP16, s);
+      // The fp16 pass itself runs front to back in `stages` slices of the ray: a ray whose optical depth over the slices
+      // done so far is beyond tau_cut cannot give weight to anything behind it (the same argument as for the refinement
+      // list), so the later slices only cover the rays that still have light.
+      const int stages =
+          (c->coarse_stages > 1 && nc % c->coarse_stages == 0 && nc / c->coarse_stages >= 8) ? c->coarse_stages : 1;
+      if (stages == 1) {
+        rc = run_mlp(c, NERF_NET_COARSE, src, dst, NERF_PREC_FP16, s);
+      } else {
+        if ((rc = c->alive[0].reserve(n * 4)) || (rc = c->alive[1].reserve(n * 4))) return rc;
+        // samples never evaluated keep 0xFEFEFEFE = -1.7e38: a hugely negative pre-activation, density 0
+        NERF_CUDA(cudaMemsetAsync(c->sigc.p, 0xFE, n * nc * 4, s));
+        uint32_t* cnt = c->sel_count.as<uint32_t>() + 8;  // one counter per stage, behind the refinement's two
+        NERF_CUDA(cudaMemsetAsync(cnt, 0, 4 * 16, s));
+        const int per = nc / stages;
+        SampleSrc part = src;
+        part.sub_n = per;
+        part.B = n * per;
+        for (int k = 0; k < stages && rc == NERF_OK; ++k) {
+          part.sub_s0 = k * per;
+          if (k > 0) {
+            NERF_CUDA(launch_coarse_alive(c->sigc.as<float>(), c->tc.as<float>(), n, nc, k * per, cam.far_, c->select_tau,
+                                          k > 1 ? c->alive[(k - 1) & 1].as<int32_t>() : nullptr,
+                                          k > 1 ? cnt + (k - 1) : nullptr, c->alive[k & 1].as<int32_t>(), cnt + k, s));
+            ++c->launches;
+            part.index = c->alive[k & 1].as<int32_t>();
+            part.count = cnt + k;
+          }
+          rc = run_mlp(c, NERF_NET_COARSE, part, dst, NERF_PREC_FP16, s);
+        }
+      }
       span_end(c, s);
       if (rc) return rc;
       span_begin(c, ST_COARSE_REFINE, s);
@@ -635,7 +666,7 @@ void nerf_destroy(nerf_ctx* c) {
       c->vmm_frames.clear();
     }
     for (DevBuf* b : {&c->dirs, &c->tc, &c->sigc, &c->wc, &c->tf, &c->sigf, &c->rgbf, &c->out, &c->in_a, &c->in_b,
-                      &c->jit, &c->uni, &c->q8[0], &c->q8[1], &c->depth, &c->acc, &c->sel_list, &c->sel_count})
+                      &c->jit, &c->uni, &c->q8[0], &c->q8[1], &c->depth, &c->acc, &c->sel_list, &c->sel_count, &c->alive[0], &c->alive[1]})
       b->release();
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
     for (int i = 0; i < 2; ++i) {

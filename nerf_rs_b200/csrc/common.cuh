@@ -49,6 +49,10 @@ struct SampleSrc {
   float origin[3];
   const int32_t* index;   // mode 1 only, nullable: sample ids of the launch slots
   const uint32_t* count;  // with index: device-resident number of slots
+  // Staged coarse pass (mlp_tc_kernel's raw-sigma instantiation only): the launch covers samples
+  // [sub_s0, sub_s0 + sub_n) of every ray (sub_n = 0: the whole ray); with `index` the rays are the listed ones
+  // (`index` holds ray ids, `count` their number) and slot i is sample sub_s0 + i % sub_n of ray index[i / sub_n].
+  int sub_s0, sub_n;
 };
 
 struct SampleDst {
@@ -134,6 +138,11 @@ cudaError_t launch_importance(const float* d_tc, const float* d_sigc, const floa
 // d_list, their number to *d_count (zeroed by the caller).
 cudaError_t launch_coarse_select(float* d_sig, const float* d_t, int64_t n_rays, int nc, float far_, float margin,
                                  float tau_cut, int32_t* d_list, uint32_t* d_count, cudaStream_t s);
+// Staged coarse pass: appends to d_list the rays (all n_rays of them, or those of d_in_list) whose optical depth over
+// samples [0, s_end) - from the pre-activations in d_sig - is still below tau_cut; the number goes to *d_count.
+cudaError_t launch_coarse_alive(const float* d_sig, const float* d_t, int64_t n_rays, int nc, int s_end, float far_,
+                                float tau_cut, const int32_t* d_in_list, const uint32_t* d_in_count, int32_t* d_list,
+                                uint32_t* d_count, cudaStream_t s);
 cudaError_t launch_weights(const float* d_sigma, const float* d_t, int64_t n_rays, int n, float far_, float* d_w,
                            cudaStream_t s);
 cudaError_t launch_quantize(const float* d_rgb, int64_t n_pixels, int channels, uint8_t* d_out, cudaStream_t s);

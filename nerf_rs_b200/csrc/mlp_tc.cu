@@ -225,7 +225,10 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
   const int64_t pair_id = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const bool want_rgb = dst.rgb != nullptr;
   const int n_layers = want_rgb ? kNumLayers : 8;
-  const int64_t n_tiles = (src.B + kTileM - 1) / kTileM;
+  // kRawSigma launches (coarse first pass) cover a slice of every ray's samples, optionally of listed rays only, whose
+  // number the previous stage left on the device
+  const int64_t B = (kRawSigma && src.count != nullptr) ? (int64_t)__ldg(src.count) * src.sub_n : src.B;
+  const int64_t n_tiles = (B + kTileM - 1) / kTileM;
   const int64_t n_quads = (n_tiles + 3) / 4;  // quad u = tiles 4u..4u+3: slot s of CTA r owns tile 4u + 2s + r
 
   if (threadIdx.x == 0) {
@@ -430,21 +433,40 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
     // The next quad's inputs are fetched two layers before they are needed: {p.xyz, -} for explicit points,
     // {dir.xyz, t} for samples along rays.  Tiles past the end run the same barrier protocol on zeros.
     float4 pre[2];
+    // kRawSigma: sample id (ray * S + s) of the prefetched row, and the ray-list entry of the row's slot one quad
+    // further on (loaded a quad early so that the dependent loads of dirs / t never wait for it inside a drain)
+    int32_t g_pre[2] = {0, 0}, idx_pre[2] = {0, 0};
+    auto load_index = [&](int64_t qd) {
+      if (kRawSigma && src.index != nullptr) {
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          const int64_t gi = (4 * qd + 2 * s + (int64_t)rank) * kTileM + row;
+          if (gi < B) idx_pre[s] = __ldg(src.index + gi / src.sub_n);
+        }
+      }
+    };
     auto prefetch = [&](int64_t qd) {
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
         const int64_t gi = (4 * qd + 2 * s + (int64_t)rank) * kTileM + row;
         pre[s] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (gi < src.B) {
-          if (src.mode == 0) {
-            pre[s] = make_float4(src.points[gi], src.points[src.B + gi], src.points[2 * src.B + gi], 0.f);
+        if (gi < B) {
+          if (kRawSigma) {
+            const int32_t r = (int32_t)(gi / src.sub_n);
+            const int32_t ray = src.index != nullptr ? idx_pre[s] : r;
+            g_pre[s] = ray * src.S + src.sub_s0 + (int32_t)(gi - (int64_t)r * src.sub_n);
+            pre[s] = make_float4(src.dirs[ray * 3 + 0], src.dirs[ray * 3 + 1], src.dirs[ray * 3 + 2], src.t[g_pre[s]]);
+          } else if (src.mode == 0) {
+            pre[s] = make_float4(src.points[gi], src.points[B + gi], src.points[2 * B + gi], 0.f);
           } else {
             const int64_t ray = gi / src.S;
             pre[s] = make_float4(src.dirs[ray * 3 + 0], src.dirs[ray * 3 + 1], src.dirs[ray * 3 + 2], src.t[gi]);
           }
         }
       }
+      load_index(qd + n_pairs);
     };
+    load_index(pair_id);
     prefetch(pair_id);
     for (int64_t qd = pair_id; qd < n_quads; qd += n_pairs) {
       int64_t g[2];
@@ -455,7 +477,8 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
       for (int s = 0; s < 2; ++s) {
         const int64_t tile = 4 * qd + 2 * s + (int64_t)rank;
         g[s] = tile * kTileM + row;
-        valid[s] = g[s] < src.B;
+        valid[s] = g[s] < B;
+        if (kRawSigma) g[s] = g_pre[s];  // where this row's density goes: ray * S + sample
         float p[3] = {pre[s].x, pre[s].y, pre[s].z};
         dir[s][0] = dir[s][1] = dir[s][2] = 0.f;
         if (src.mode == 0) {
@@ -738,9 +761,16 @@ cudaError_t init_mlp_tc() {  // once per process and device, at context creation
   return cudaSuccess;
 }
 
-cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
+cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src_in, const SampleDst& dst, int sm_count,
                           cudaStream_t s) {
-  if (src.B == 0) return cudaSuccess;
+  SampleSrc src = src_in;
+  if (dst.sigma_floor < 0.0f) {  // raw-sigma launches address samples as (ray, slice): default = the whole ray
+    if (src.mode != 1) return cudaErrorInvalidValue;
+    if (src.sub_n <= 0) { src.sub_s0 = 0; src.sub_n = src.S; }
+  } else if (src.index != nullptr || src.sub_n != 0) {
+    return cudaErrorInvalidValue;  // ray lists and slices exist in the raw-sigma instantiation only
+  }
+  if (src.B == 0) return cudaSuccess;  // with a device-resident count, B is its upper bound
   const int64_t n_tiles = (src.B + kTileM - 1) / kTileM;
   const int64_t n_quads = (n_tiles + 3) / 4;  // a CTA pair works on four tiles at a time
   const int64_t max_pairs = sm_count / 2;

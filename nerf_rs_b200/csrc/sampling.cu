@@ -370,6 +370,53 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) coarse_select_kernel(float*
   }
 }
 
+// Staged coarse pass: which rays still have light after their first s_end coarse samples?  One warp per
+// candidate ray (all rays, or the survivors of the previous stage), optical depth from the fp16 pre-activations as in
+// coarse_select_kernel; survivors are appended to `list` (one reservation per CTA of 8 rays).
+__global__ void __launch_bounds__(kWarpsPerCta * 32) coarse_alive_kernel(const float* __restrict__ sig,
+                                                                         const float* __restrict__ t, int64_t n_rays,
+                                                                         int nc, int s_end, float far_, float tau_cut,
+                                                                         const int32_t* __restrict__ in_list,
+                                                                         const uint32_t* __restrict__ in_count,
+                                                                         int32_t* __restrict__ list,
+                                                                         uint32_t* __restrict__ count) {
+  __shared__ uint32_t s_alive[kWarpsPerCta], s_base;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t n = in_list != nullptr ? (int64_t)*in_count : n_rays;
+  for (int64_t c0 = blockIdx.x * (int64_t)kWarpsPerCta; c0 < n; c0 += (int64_t)gridDim.x * kWarpsPerCta) {
+    const int64_t c = c0 + warp;
+    int64_t ray = -1;
+    bool alive = false;
+    if (c < n) {
+      ray = in_list != nullptr ? (int64_t)in_list[c] : c;
+      float tau = 0.0f;
+      for (int i = lane; i < s_end; i += 32) {
+        const float ti = t[ray * nc + i];
+        float delta = (i + 1 < nc) ? (t[ray * nc + i + 1] - ti) : (far_ - ti);
+        if (delta < 0.0f) delta = 0.0f;
+        tau += fmaxf(sig[ray * nc + i], 0.0f) * delta;
+      }
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) tau += __shfl_xor_sync(kFull, tau, d);
+      alive = !(tau >= tau_cut);  // NaN keeps the ray
+    }
+    if (lane == 0) s_alive[warp] = alive ? 1u : 0u;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t sum = 0;
+      for (int w = 0; w < kWarpsPerCta; ++w) {
+        const uint32_t a = s_alive[w];
+        s_alive[w] = sum;
+        sum += a;
+      }
+      s_base = sum ? atomicAdd(count, sum) : 0u;
+    }
+    __syncthreads();
+    if (alive && lane == 0) list[s_base + s_alive[warp]] = (int32_t)ray;
+    __syncthreads();
+  }
+}
+
 // compute_weights alone (stage parity entry point).
 __global__ void __launch_bounds__(kWarpsPerCta * 32) weights_kernel(const float* __restrict__ sigma,
                                                                     const float* __restrict__ t, int64_t n_rays,
@@ -495,6 +542,15 @@ cudaError_t launch_coarse_select(float* d_sig, const float* d_t, int64_t n_rays,
   if (n_rays == 0) return cudaSuccess;
   coarse_select_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, 0, s>>>(d_sig, d_t, n_rays, nc, far_,
                                                                                     margin, tau_cut, d_list, d_count);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_coarse_alive(const float* d_sig, const float* d_t, int64_t n_rays, int nc, int s_end, float far_,
+                                float tau_cut, const int32_t* d_in_list, const uint32_t* d_in_count, int32_t* d_list,
+                                uint32_t* d_count, cudaStream_t s) {
+  if (n_rays == 0) return cudaSuccess;
+  coarse_alive_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, 0, s>>>(
+      d_sig, d_t, n_rays, nc, s_end, far_, tau_cut, d_in_list, d_in_count, d_list, d_count);
   return cudaGetLastError();
 }
 

@@ -17,7 +17,7 @@ CAM = os.path.join(nb.DATA_ROOT, "tf_reference_samples.json")
 
 
 def render(env, cam, W, H, prec="mixed", stages=True, reps=1):
-    for k in ("NERF_B200_COARSE_SELECT", "NERF_B200_SELECT_MARGIN", "NERF_B200_SELECT_TAU"):
+    for k in ("NERF_B200_COARSE_SELECT", "NERF_B200_SELECT_MARGIN", "NERF_B200_SELECT_TAU", "NERF_B200_COARSE_STAGES"):
         os.environ.pop(k, None)
     os.environ.update(env)
     r = nb.Renderer(nb.DATA_ROOT)
@@ -67,6 +67,8 @@ def main():
               f"{t['mlp_fine_ms']:.2f}, total {t['total_ms']:.2f}", flush=True)
         compare(f"pose {ci} default", full, render({}, cam, W, H, reps=2 if ci == 0 else 1))
         if ci == 0:
+            for stages in ("1", "2", "4", "8"):
+                compare(f"stages {stages}", full, render({"NERF_B200_COARSE_STAGES": stages}, cam, W, H, reps=3))
             for margin in ("0.5", "0.25", "0.1", "0.03", "0.0"):
                 compare(f"margin {margin}", full, render({"NERF_B200_SELECT_MARGIN": margin}, cam, W, H))
             for tau in ("10.5", "9.5", "9.0", "8.0"):

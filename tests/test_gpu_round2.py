@@ -84,7 +84,7 @@ def test_philox_default_sampling_at_reference_counts(renderer, cam, onets, ocam,
 
 def _fresh(env):
     keys = ("NERF_B200_COARSE_SELECT", "NERF_B200_CHUNK_RAYS", "NERF_B200_SELECT_MARGIN", "NERF_B200_SELECT_TAU",
-            "NERF_B200_SKIP_EMPTY")
+            "NERF_B200_SKIP_EMPTY", "NERF_B200_COARSE_STAGES")
     saved = {k: os.environ.pop(k, None) for k in keys}
     os.environ.update(env)
     try:
@@ -238,3 +238,28 @@ def test_striped_views_assemble_the_frame_bit_for_bit(renderer, cam):
         renderer.render_striped(cam, W, H, np.zeros((n, 3), np.float32), 0, 2, 0)
     with pytest.raises(nb.NerfError):
         renderer.render_striped(cam, W, H, np.zeros((n, 3), np.float32), W, 2, 2)
+
+
+def test_staged_coarse_pass_is_invisible(renderer, cam):
+    """mixed mode: the fp16 coarse pass runs front to back in slices of the ray and later slices skip the rays that have
+    gone opaque (optical depth beyond tau_cut: every weight behind is exactly 0, lib.rs:276-279).  Fine sample positions,
+    coarse weights and pixels must not depend on the number of slices - one launch over every sample included."""
+    W = H = 200
+    want = {}
+    for stages in ("1", "2", "4", "8"):
+        r = _fresh({"NERF_B200_COARSE_STAGES": stages})
+        try:
+            for mode, seed in ((nb.SAMPLING_DET, 0), (nb.SAMPLING_PHILOX, 17)):
+                img, st = r.render_image(cam, W, H, 64, 128, precision="mixed", mode=mode, seed=seed, stages=True)
+                assert np.isfinite(img).all() and np.isfinite(st["sigma_c"]).all() and (st["sigma_c"] >= 0).all()
+                if stages == "1":
+                    want[mode] = (img, st["w_c"], st["t_f"])
+                else:
+                    assert (img == want[mode][0]).all() and (st["w_c"] == want[mode][1]).all(), stages
+                    assert (st["t_f"] == want[mode][2]).all(), stages
+            # sample counts the slices do not divide fall back to one launch and still render
+            odd = r.render_image(cam, 32, 24, 20, 24, precision="mixed")
+            assert (odd == renderer.render_image(cam, 32, 24, 20, 24, precision="mixed")).all()
+        finally:
+            r.close()
+    assert (renderer.render_image(cam, W, H, 64, 128, precision="mixed") == want[nb.SAMPLING_DET][0]).all()
