@@ -263,3 +263,44 @@ def test_staged_coarse_pass_is_invisible(renderer, cam):
         finally:
             r.close()
     assert (renderer.render_image(cam, W, H, 64, 128, precision="mixed") == want[nb.SAMPLING_DET][0]).all()
+
+
+def test_fixed_size_importance_kernel_equals_the_generic_one(renderer, cam):
+    """64 + 128 samples (the reference's counts) run importance_fixed_kernel: unrolled folds, verified rank hints,
+    slot-ordered stores.  NERF_B200_GENERIC_IMPORTANCE=1 forces the generic kernel on the same context: fine sample
+    positions must agree bit for bit - sorted input (fast merge) and unsorted input (sort + rank merge) alike - and the
+    oracle must agree with both."""
+    def both(fn):
+        os.environ.pop("NERF_B200_GENERIC_IMPORTANCE", None)
+        fixed = fn()
+        os.environ["NERF_B200_GENERIC_IMPORTANCE"] = "1"
+        try:
+            return fixed, fn()
+        finally:
+            os.environ.pop("NERF_B200_GENERIC_IMPORTANCE", None)
+
+    W = H = 160
+    for kw in (dict(mode=nb.SAMPLING_DET), dict(mode=nb.SAMPLING_PHILOX, seed=23)):
+        (a, sa), (b, sb) = both(lambda: renderer.render_image(cam, W, H, 64, 128, precision="mixed", stages=True, **kw))
+        assert (sa["t_f"] == sb["t_f"]).all() and (sa["w_c"] == sb["w_c"]).all() and (a == b).all(), kw
+        assert (np.diff(sa["t_f"], axis=1) >= 0).all()
+    # the stage entry point: regular u (fast merge), random u (fine samples unsorted), duplicates and ties, empty
+    # weights (flat cdf), and coarse samples that arrive unsorted
+    rng = np.random.default_rng(41)
+    n, cnt, rays = 64, 128, 300
+    t = np.sort(rng.uniform(2, 6, (rays, n)).astype(np.float32), axis=1)
+    w = (rng.uniform(0, 1, (rays, n)) ** 6).astype(np.float32)
+    w[:7] = 0
+    w[7:14, 10:] = 0
+    grid = np.tile(((np.arange(cnt) + 0.5) / cnt).astype(np.float32), (rays, 1))
+    dup = np.repeat(rng.uniform(0, 1, (rays, cnt // 4)).astype(np.float32), 4, axis=1)
+    shuffled = t.copy()
+    shuffled[::3] = shuffled[::3, ::-1]
+    cases = [(t, grid), (t, rng.uniform(0, 1, (rays, cnt)).astype(np.float32)), (t, np.sort(dup, axis=1)), (t, dup),
+             (shuffled, grid)]
+    for tt, u in cases:
+        got, gen = both(lambda: renderer.sample_importance(tt, w, u))
+        assert (got == gen).all()
+        want = np.stack([np.sort(np.concatenate([tt[i], O.sample_importance(tt[i], w[i], u[i])]), kind="stable")
+                         for i in range(0, rays, 5)])
+        assert np.abs(got[::5] - want).max() < 2e-6 and (np.diff(got, axis=1) >= 0).all()
