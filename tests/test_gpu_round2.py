@@ -140,6 +140,12 @@ def test_chunked_render_equals_single_chunk(renderer, cam):
                 b = small.render_image(cam, W, H, nc, nf, precision=prec, ray_begin=31, ray_end=333, **(
                     kw if kw["mode"] != nb.SAMPLING_ARRAYS else dict(mode=nb.SAMPLING_ARRAYS, jitter=jit[31:333], u=u[31:333])))
                 assert (a == b).all(), (prec, kw["mode"], "range")
+        # the reference's sample counts: chunks together with the staged coarse pass (per-chunk ray lists and counters)
+        # and the fixed-size importance kernel
+        for kw in (dict(mode=nb.SAMPLING_DET), dict(mode=nb.SAMPLING_PHILOX, seed=9)):
+            a = renderer.render_image(cam, W, H, 64, 128, precision="mixed", **kw)
+            b = small.render_image(cam, W, H, 64, 128, precision="mixed", **kw)
+            assert (a == b).all(), ("64+128", kw["mode"])
         ra, da, aa = renderer.render_aux(cam, W, H, nc, nf, precision="fp32")
         rb, db, ab = small.render_aux(cam, W, H, nc, nf, precision="fp32")
         assert (ra == rb).all() and (da == db).all() and (aa == ab).all()
