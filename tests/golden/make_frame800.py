@@ -2,7 +2,9 @@
 deterministic sampling, tf_reference camera) - the reference render the north star's image criterion names
 (render_image, src/lib.rs:474-565).  About 7 core-hours of CPU work, so the frame is rendered in bands of 8 rows with
 a resumable scratch file (tests/golden/_frame_800_partial.npy, git-ignored):
-    python tests/golden/make_frame800.py [threads]
+    python tests/golden/make_frame800.py [threads] [det | philox SEED]
+`philox SEED` writes frame_800_philox<SEED>.npz instead: the same frame with the Philox jitter of the product's default
+sampling mode (the reproducible stand-in for the reference's OS-seeded thread_rng, lib.rs:243,332).
 
 Stored as: `white` = bit mask of pixels that are exactly (1,1,1) in f32 (background: zero density along the whole
 ray), `rgb` = the f32 values of all other pixels in pixel-index order; `sha256` of the f32 frame bytes.
@@ -40,10 +42,14 @@ def unpack(z):
 
 def main():
     threads = int(sys.argv[1]) if len(sys.argv) > 1 else 0
+    philox = len(sys.argv) > 3 and sys.argv[2] == "philox"
+    seed = int(sys.argv[3]) if philox else 0
+    tag = f"_philox{seed}" if philox else ""
+    kw = dict(mode=O.SAMPLING_PHILOX, seed=seed) if philox else {}
     cam = O.camera_from_json(os.path.join(DATA, "tf_reference_samples.json"))
     oc, of = O.Network(os.path.join(DATA, "coarse")), O.Network(os.path.join(DATA, "fine"))
-    part = os.path.join(HERE, "_frame_800_partial.npy")
-    done_f = os.path.join(HERE, "_frame_800_done.npy")
+    part = os.path.join(HERE, f"_frame_800{tag}_partial.npy")
+    done_f = os.path.join(HERE, f"_frame_800{tag}_done.npy")
     frame = np.load(part) if os.path.exists(part) else np.zeros((W * H, 3), np.float32)
     done = np.load(done_f) if os.path.exists(done_f) else np.zeros(H // BAND, bool)
     t0 = time.time()
@@ -51,15 +57,17 @@ def main():
         if done[b]:
             continue
         rb, re_ = b * BAND * W, (b + 1) * BAND * W
-        frame[rb:re_] = O.render(oc, of, cam, W, H, 64, 128, ray_begin=rb, ray_end=re_, threads=threads)
+        frame[rb:re_] = O.render(oc, of, cam, W, H, 64, 128, ray_begin=rb, ray_end=re_, threads=threads, **kw)
         done[b] = True
         np.save(part, frame)
         np.save(done_f, done)
         print(f"band {b + 1}/{H // BAND} done, {time.time() - t0:.0f} s", flush=True)
     out = pack(frame)
     assert np.array_equal(unpack(out), frame)
-    np.savez_compressed(os.path.join(HERE, "frame_800.npz"), **out)
-    print("frame_800.npz written; sha256", out["sha256"], "non-white pixels", len(out["rgb"]))
+    if philox:
+        out["seed"] = seed
+    np.savez_compressed(os.path.join(HERE, f"frame_800{tag}.npz"), **out)
+    print(f"frame_800{tag}.npz written; sha256", out["sha256"], "non-white pixels", len(out["rgb"]))
 
 
 if __name__ == "__main__":

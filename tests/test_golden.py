@@ -112,3 +112,45 @@ def test_oracle_reproduces_full_frame_fixture(onets, ocam):
         rb = row * 800 + col
         rgb = O.render(onets[0], onets[1], ocam, 800, 800, 64, 128, ray_begin=rb, ray_end=rb + 64)
         assert np.abs(rgb - frame[rb:rb + 64]).max() <= 2e-6
+
+
+ORBIT = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "render_800_orbit_bands.npz"))
+
+
+def _orbit_cams(make):
+    """The fixture's cameras through `make(near, far, origin, forward, up, hwf)`; poses as nerf_rs_b200.orbit_poses."""
+    import nerf_rs_b200 as nb
+    from .conftest import CAM_JSON
+    poses = nb.orbit_poses(CAM_JSON, int(ORBIT["n_views"]))
+    return {int(k): make(poses[k]["near"], poses[k]["far"], poses[k]["camera_origin"], poses[k]["camera_forward"],
+                         poses[k]["camera_up"], poses[k]["hwf"]) for k in ORBIT["poses"]}
+
+
+def test_oracle_reproduces_orbit_bands(onets):
+    """Drift guard for tests/golden/render_800_orbit_bands.npz (make_band_orbit.py): 64 rays of each pose."""
+    rb = int(ORBIT["ray_begin"]) + 2 * 800 + 380
+    for k, cam in _orbit_cams(O.camera_from_values).items():
+        rgb = O.render(onets[0], onets[1], cam, 800, 800, 64, 128, ray_begin=rb, ray_end=rb + 64)
+        off = rb - int(ORBIT["ray_begin"])
+        assert np.abs(rgb - ORBIT[f"rgb_{k}"][off:off + 64]).max() <= 2e-6, k
+
+
+@pytest.mark.gpu
+def test_gpu_orbit_bands_against_the_oracle(renderer):
+    """The image bound away from the reference pose: rows 396..403 of the 800x800 frame from two other cameras of the
+    orbit (6 400 rays each, through the object), against the CPU oracle with identical deterministic sample positions.
+    The reference's pipeline is discontinuous in its own rounding on thin structures, so a pixel or two
+    of a band may leave 2/255 even in the order-faithful f32 mode; what is held is at most 2 such pixels per band and
+    the PSNR."""
+    import nerf_rs_b200 as nb
+    rb, re_ = int(ORBIT["ray_begin"]), int(ORBIT["ray_end"])
+    for k, cam in _orbit_cams(nb.camera_from_values).items():
+        want = ORBIT[f"rgb_{k}"]
+        assert want.std() > 0.05  # the band crosses the object
+        for prec, psnr_min in (("fp32", 85.0), ("fp16x3", 80.0), ("mixed", 70.0)):
+            got = renderer.render_image(cam, 800, 800, 64, 128, precision=prec, ray_begin=rb, ray_end=re_)
+            d = np.abs(got - want).max(axis=1)
+            psnr = 10 * np.log10(1.0 / max(float(np.mean((got.astype(np.float64) - want) ** 2)), 1e-20))
+            print(f"orbit pose {k} band vs oracle, {prec}: max {d.max() * 255:.3f}/255, pixels > 2/255: "
+                  f"{int((d > 2 / 255).sum())}, PSNR {psnr:.1f} dB")
+            assert int((d > 2.0 / 255.0).sum()) <= 2 and psnr >= psnr_min, (k, prec, float(d.max()) * 255, psnr)
