@@ -44,6 +44,8 @@ PRECISION_NOTE = {
     "fp16": "fp16: both networks single-pass fp16 operands, f32 accumulate; PSNR ~71 dB, ~100 of 640 000 pixels (thin "
             "structures) above 2/255",
     "fp16x3": "fp16x3: both networks split-fp16 operands, 3 tensor-core MMAs per product",
+    "tf32": "tf32: both networks tcgen05 kind::tf32 (32-bit containers, 10-bit mantissa), f32 accumulate; the accuracy of "
+            "fp16 at less than half its speed",
 }
 # dram__bytes_read.sum + dram__bytes_write.sum of the fine-pass launch, 800x800 c64+f128: a CONSTANT copied from one
 # `ncu --set full` capture (file below), not measured by this run
@@ -537,7 +539,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--precision", default="mixed", choices=["fp16", "bf16", "mixed", "fp16x3", "fp32"])
+    ap.add_argument("--precision", default="mixed", choices=["fp16", "bf16", "tf32", "mixed", "fp16x3", "fp32"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],

@@ -43,10 +43,11 @@ typedef enum {
 typedef enum {
   NERF_PREC_FP32 = 0, /* CUDA-core path; per-element sum order identical to network.rs:134-143 */
   NERF_PREC_BF16 = 1, /* tcgen05 kind::f16, bf16 operands, f32 accumulate in TMEM */
-  NERF_PREC_FP16 = 2, /* tcgen05 kind::f16, fp16 operands: the 10-bit operand mantissa of tf32 at twice its rate.  This
-                       * is what serves the north star's "tf32 mode"; there is no kind::tf32 kernel. */
-  NERF_PREC_TF32 = 3, /* reserved, NOT a mode: every entry point answers NERF_E_UNSUPPORTED (round 1 silently ran the
-                       * FP16 path under this name).  Ask for NERF_PREC_FP16. */
+  NERF_PREC_FP16 = 2, /* tcgen05 kind::f16, fp16 operands: the 10-bit operand mantissa of tf32 at twice its rate */
+  NERF_PREC_TF32 = 3, /* tcgen05 kind::tf32, operands in 32-bit containers (8-bit exponent, 10-bit mantissa), f32
+                       * accumulate in TMEM (mlp_tc_tf32.cu).  On these networks it computes what FP16 computes at
+                       * less than half the speed; it is the north star's "tf32 mode", kept for completeness.  (Round 1
+                       * silently ran the FP16 path under this name.) */
   NERF_PREC_FP16X3 = 4 /* tcgen05 kind::f16, every operand split x = hi + lo (two fp16), three MMAs per product
                         * (hi.hi + lo.hi + hi.lo), f32 accumulate: ~22-bit operands, f32-class results at a third
                         * of the FP16 rate.  The mode that meets the reference-accuracy bounds on the tensor cores. */

@@ -19,8 +19,8 @@ LIB_PATH = os.path.join(_HERE, "libnerf_b200.so")
 DATA_ROOT = os.path.join(os.path.dirname(_HERE), "data", "lego_rust")
 
 PREC_FP32, PREC_BF16, PREC_FP16, PREC_TF32, PREC_FP16X3, PREC_MIXED = 0, 1, 2, 3, 4, 5
-# PREC_TF32 is reserved by the ABI and answers E_UNSUPPORTED: there is no kind::tf32 kernel, fp16 serves that slot
-PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "fp16": PREC_FP16, "fp16x3": PREC_FP16X3, "mixed": PREC_MIXED}
+PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "fp16": PREC_FP16, "tf32": PREC_TF32, "fp16x3": PREC_FP16X3,
+              "mixed": PREC_MIXED}
 NET_COARSE, NET_FINE = 0, 1
 SAMPLING_DET, SAMPLING_PHILOX, SAMPLING_ARRAYS = 0, 1, 2
 

@@ -64,6 +64,7 @@ struct DeviceNet {
   NetF32 f32{};
   TcWeights tc[2];        // [0] bf16, [1] fp16 pre-swizzled operand tiles (mlp_tc.cu)
   TcWeights tcx3;         // fp16 hi / lo split tiles of the fp16x3 mode (mlp_tc_x3.cu)
+  TcWeights tctf32;       // tf32 tiles (mlp_tc_tf32.cu)
 };
 
 enum StageKind { ST_SAMPLING = 0, ST_MLP_COARSE, ST_MLP_FINE, ST_COMPOSITE, ST_COARSE_REFINE, ST_COUNT };
@@ -162,7 +163,7 @@ int upload_network(const TensorMap& t, DeviceNet* net, const std::vector<uint8_t
   net->f32.w_alpha = dptr[22]; net->f32.b_alpha = dptr[23];
   // Pre-swizzled 16-bit operand tiles for the tensor-core kernel, one set per operand format.
   for (int fmt = 0; fmt < kNumTcFormats; ++fmt) {
-    TcWeights* w = fmt == 2 ? &net->tcx3 : &net->tc[fmt];
+    TcWeights* w = fmt == 3 ? &net->tctf32 : (fmt == 2 ? &net->tcx3 : &net->tc[fmt]);
     int rc = images ? upload_tc_weights(images[fmt].data(), images[fmt].size(), fmt, t, w) : build_tc_weights(t, fmt, w);
     if (rc != NERF_OK) return rc;
   }
@@ -211,6 +212,7 @@ int create_common(const TensorMap& coarse, const TensorMap& fine, int device, ne
   cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = init_mlp_tc();  // function attributes, once per device
   if (e == cudaSuccess) e = init_mlp_tc_x3();
+  if (e == cudaSuccess) e = init_mlp_tc_tf32();
   if (e == cudaSuccess) e = init_sampling();
   if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev_begin);
   if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev_end);
@@ -282,9 +284,8 @@ int run_mlp(nerf_ctx* c, int net, const SampleSrc& src, const SampleDst& dst, in
       e = launch_mlp_tc(c->nets[net].tc[0], src, dst, c->sm_count, s);
       break;
     case NERF_PREC_TF32:
-      set_error("NERF_PREC_TF32 is not a mode of this library (no kind::tf32 kernel): use NERF_PREC_FP16, the same "
-                "10-bit operand mantissa at twice the rate");
-      return NERF_E_UNSUPPORTED;
+      e = launch_mlp_tc_tf32(c->nets[net].tctf32, src, dst, c->sm_count, s);
+      break;
     case NERF_PREC_FP16:
       e = launch_mlp_tc(c->nets[net].tc[1], src, dst, c->sm_count, s);
       break;
@@ -679,6 +680,7 @@ void nerf_destroy(nerf_ctx* c) {
       if (n.blob) cudaFree(n.blob);
       for (auto& t : n.tc) free_tc_weights(&t);
       free_tc_weights(&n.tcx3);
+      free_tc_weights(&n.tctf32);
     }
     for (auto& sp : c->spans) {
       cudaEventDestroy(sp.a);

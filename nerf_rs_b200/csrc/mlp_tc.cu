@@ -695,6 +695,10 @@ void build_tc_image(const TensorMap& t, int fmt, std::vector<uint8_t>* out) {
     build_tc_x3_image(t, out);
     return;
   }
+  if (fmt == 3) {
+    build_tc_tf32_image(t, out);
+    return;
+  }
   std::vector<uint8_t>& img = *out;
   img.clear();
   img.reserve(1500 * 1024);
@@ -717,6 +721,7 @@ void build_tc_image(const TensorMap& t, int fmt, std::vector<uint8_t>* out) {
 }
 
 size_t tc_image_bytes(int fmt) {
+  if (fmt == 3) return tc_tf32_image_bytes();
   size_t n = 0;
   for (int l = 0; l < kNumLayers; ++l) {
     const int kblocks = l == 0 ? 1 : ((l == 5 || l == 9) ? 5 : 4);  // 64-row K-blocks, encodings padded to 64

@@ -23,7 +23,7 @@ struct alignas(16) TcConsts {
 struct TcWeights {
   uint8_t* d_chunks = nullptr;
   size_t bytes = 0;
-  int fmt = 0;  // 0 = bf16, 1 = fp16, 2 = fp16 hi/lo split (fp16x3)
+  int fmt = 0;  // 0 = bf16, 1 = fp16, 2 = fp16 hi/lo split (fp16x3), 3 = tf32
   TcConsts consts;
 };
 
@@ -31,13 +31,17 @@ struct TcWeights {
 // between the CTAs of a pair, the K-block size, the swizzle or the hi/lo scaling changes: weight cache files carry its
 // hash in their version word (weight_cache.cu) and files of another layout are refused.
 constexpr char kTcLayoutTag[] =
-    "r2:kmajor-sw128;kblock64;n256(viewdirs128);order=d0:pe|d1-4:4|d5:pe+4|d6-7:4|bott:4|view:4+pe4;x3=hi,lo*2^11 per kblock";
+    "r2:kmajor-sw128;kblock64;n256(viewdirs128);order=d0:pe|d1-4:4|d5:pe+4|d6-7:4|bott:4|view:4+pe4;x3=hi,lo*2^11 per kblock;"
+    "tf32=kblock32,rna,same order";
 
-// Operand formats: 0 = bf16, 1 = fp16 (mlp_tc.cu), 2 = fp16 hi / lo split, a hi and a lo chunk per K-block (mlp_tc_x3.cu).
-constexpr int kNumTcFormats = 3;
+// Operand formats: 0 = bf16, 1 = fp16 (mlp_tc.cu), 2 = fp16 hi / lo split, a hi and a lo chunk per K-block (mlp_tc_x3.cu),
+// 3 = tf32 in 32-bit containers, K-blocks of 32 (mlp_tc_tf32.cu).
+constexpr int kNumTcFormats = 4;
 // Host side (no GPU needed): the chunk stream of one network in one format, and the epilogue's f32 tables.
 void build_tc_image(const TensorMap& t, int fmt, std::vector<uint8_t>* out);
 void build_tc_x3_image(const TensorMap& t, std::vector<uint8_t>* out);
+void build_tc_tf32_image(const TensorMap& t, std::vector<uint8_t>* out);
+size_t tc_tf32_image_bytes();
 void fill_tc_consts(const TensorMap& t, TcConsts* c);
 size_t tc_image_bytes(int fmt);  // length of that stream: the kernels' bulk copies read exactly this much
 // Device upload of a chunk stream (built just now, or read from a weight cache file).
@@ -47,9 +51,12 @@ void free_tc_weights(TcWeights* w);
 // Opt the kernels into their dynamic shared memory size (once per device, at context creation).
 cudaError_t init_mlp_tc();
 cudaError_t init_mlp_tc_x3();
+cudaError_t init_mlp_tc_tf32();
 cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
                           cudaStream_t s);
 cudaError_t launch_mlp_tc_x3(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
                              cudaStream_t s);
+cudaError_t launch_mlp_tc_tf32(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
+                               cudaStream_t s);
 
 }  // namespace nerf

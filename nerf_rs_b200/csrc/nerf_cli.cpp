@@ -28,7 +28,7 @@ namespace {
 void usage() {
   std::printf(
       "usage: nerf_cli [--weights DIR] [--camera JSON] [--width W] [--height H] [--nc N] [--nf N]\n"
-      "                [--precision fp32|bf16|fp16|fp16x3|mixed] [--det | --seed S] [--device D] [--gpus N]\n"
+      "                [--precision fp32|bf16|fp16|tf32|fp16x3|mixed] [--det | --seed S] [--device D] [--gpus N]\n"
       "                [--cache FILE] [--out FILE]\n"
       "defaults reproduce the reference CLI: 256x256, 64 coarse + 128 fine samples, output.ppm\n");
 }
@@ -74,6 +74,7 @@ int main(int argc, char** argv) {
       if (p == "fp32") precision = NERF_PREC_FP32;
       else if (p == "bf16") precision = NERF_PREC_BF16;
       else if (p == "fp16") precision = NERF_PREC_FP16;
+      else if (p == "tf32") precision = NERF_PREC_TF32;
       else if (p == "fp16x3") precision = NERF_PREC_FP16X3;
       else if (p == "mixed") precision = NERF_PREC_MIXED;
       else { std::fprintf(stderr, "nerf_cli: unknown precision %s\n", p.c_str()); return 2; }

@@ -42,6 +42,7 @@ pub struct NerfTensor {
 pub const PREC_FP32: c_int = 0;
 pub const PREC_BF16: c_int = 1;
 pub const PREC_FP16: c_int = 2;
+pub const PREC_TF32: c_int = 3;
 pub const PREC_FP16X3: c_int = 4;
 pub const PREC_MIXED: c_int = 5;
 pub const NET_COARSE: c_int = 0;

@@ -14,10 +14,10 @@ import nerf_rs_b200 as nb
 
 pytestmark = pytest.mark.gpu
 
-SIG_TOL = {"fp32": 2e-4, "fp16": 4e-2, "bf16": 3e-1, "fp16x3": 3e-4}  # max: single samples at a ReLU knee
-SIG_P99 = {"fp32": 1e-4, "fp16": 5e-3, "bf16": 4e-2, "fp16x3": 1e-4}  # 99th percentile of the same error
-RGB_TOL = {"fp32": 2e-5, "fp16": 6e-3, "bf16": 6e-2, "fp16x3": 1e-4}
-ROUND = {"fp16": O.ROUND_FP16, "bf16": O.ROUND_BF16}
+SIG_TOL = {"fp32": 2e-4, "fp16": 4e-2, "bf16": 3e-1, "tf32": 4e-2, "fp16x3": 3e-4}  # max: single samples at a ReLU knee
+SIG_P99 = {"fp32": 1e-4, "fp16": 5e-3, "bf16": 4e-2, "tf32": 5e-3, "fp16x3": 1e-4}  # 99th percentile of the same error
+RGB_TOL = {"fp32": 2e-5, "fp16": 6e-3, "bf16": 6e-2, "tf32": 6e-3, "fp16x3": 1e-4}
+ROUND = {"fp16": O.ROUND_FP16, "bf16": O.ROUND_BF16, "tf32": O.ROUND_TF32}
 
 
 def _golden_inputs(golden):
@@ -49,7 +49,7 @@ def _check(prec, rgb, sig, rgb_ref, sig_ref, scale=1.0):
     assert dc.max() <= RGB_TOL[prec] * scale, (prec, "rgb", float(dc.max()))
 
 
-@pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16", "fp16x3"])
+@pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16", "tf32", "fp16x3"])
 def test_forward_batch_golden_json(renderer, golden, prec):
     """The reference's own unit test (lib.rs:753-916) against the GPU path: 1e-2 abs is its tolerance; sigma in the
     16-bit modes is held to the relative bound above instead (sigma reaches 213 here)."""
@@ -66,7 +66,7 @@ def test_forward_batch_golden_json(renderer, golden, prec):
         _check(prec, rgb, sig, want_c, want_s)
 
 
-@pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16", "fp16x3"])
+@pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16", "tf32", "fp16x3"])
 @pytest.mark.parametrize("n", [1, 127, 128, 129, 255, 257, 1000, 4096 + 77])
 def test_forward_batch_random_vs_oracle(renderer, onets, ocam, prec, n):
     """Ragged batch sizes around the 64 / 128-sample tiles, both networks."""
@@ -77,7 +77,7 @@ def test_forward_batch_random_vs_oracle(renderer, onets, ocam, prec, n):
         _check(prec, rgb, sig, rgb_ref, sig_ref)
 
 
-@pytest.mark.parametrize("prec", ["fp16", "bf16"])
+@pytest.mark.parametrize("prec", ["fp16", "bf16", "tf32"])
 def test_tensor_core_matches_rounding_emulation(renderer, onets, ocam, prec):
     """Against the oracle run with the same operand rounding the kernel applies, the only difference left is
     the f32 accumulation order inside the tensor core: an order of magnitude tighter than against exact f32."""
@@ -99,11 +99,17 @@ def test_forward_batch_empty_and_errors(renderer):
         renderer.coarse.forward_batch(np.zeros((3, 4), np.float32), np.zeros((3, 3), np.float32))
     with pytest.raises(nb.NerfError):
         renderer.coarse.forward_batch(np.zeros((3, 4), np.float32), np.zeros((4, 3), np.float32), precision=9)
-    # NERF_PREC_TF32 is reserved, not an alias: there is no kind::tf32 kernel and nothing else runs under that name
-    with pytest.raises(nb.NerfError) as e:
-        renderer.coarse.forward_batch(np.zeros((3, 4), np.float32), np.zeros((4, 3), np.float32), precision=nb.PREC_TF32)
-    assert e.value.code == nb.E_UNSUPPORTED and "NERF_PREC_FP16" in str(e.value)
-    assert "tf32" not in nb.PRECISIONS
+    # NERF_PREC_TF32 is a mode of its own (tcgen05 kind::tf32, mlp_tc_tf32.cu), not an alias of fp16 as in round 1: the
+    # two agree to operand rounding but not bit for bit (other K-blocking, other accumulation order)
+    rng = np.random.default_rng(5)
+    pts = rng.uniform(-1.2, 1.2, (3, 600)).astype(np.float32)
+    dirs = rng.normal(size=(600, 3)).astype(np.float32)
+    dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+    ct, st = renderer.fine.forward_batch(pts, dirs, precision="tf32")
+    ch, sh = renderer.fine.forward_batch(pts, dirs, precision="fp16")
+    assert np.isfinite(ct).all() and np.isfinite(st).all() and st.max() > 1.0
+    assert np.abs(ct - ch).max() < 6e-3 and (np.abs(st - sh) <= 4e-2 * np.maximum(1, np.abs(sh))).all()
+    assert not (np.array_equal(ct, ch) and np.array_equal(st, sh))
 
 
 # ----------------------------------------------------------------------------------------- stage-wise parity
@@ -173,7 +179,7 @@ def test_render_fp32_parity_with_stages(renderer, cam, onets, ocam):
     assert np.abs(got - want).max() < 2e-3 and _psnr(got, want) > 70.0
 
 
-@pytest.mark.parametrize("prec,psnr_min", [("fp16", 50.0), ("bf16", 45.0)])
+@pytest.mark.parametrize("prec,psnr_min", [("fp16", 50.0), ("bf16", 45.0), ("tf32", 50.0)])
 def test_render_tensor_core_psnr(renderer, cam, onets, ocam, prec, psnr_min):
     """North star: PSNR >= 45 dB against the reference render with identical non-jittered samples."""
     W = H = 32
@@ -381,7 +387,7 @@ def test_context_from_weight_cache_is_bit_identical(renderer, cam, tmp_path):
         pts = rng.uniform(-1.5, 1.5, (3, 777)).astype(np.float32)
         dirs = rng.normal(size=(777, 3)).astype(np.float32)
         dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
-        for prec in ("fp32", "bf16", "fp16", "fp16x3"):
+        for prec in ("fp32", "bf16", "fp16", "tf32", "fp16x3"):
             for a, b in ((renderer.coarse, r2.coarse), (renderer.fine, r2.fine)):
                 ra, sa = a.forward_batch(pts, dirs, precision=prec)
                 rb, sb = b.forward_batch(pts, dirs, precision=prec)

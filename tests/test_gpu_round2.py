@@ -43,10 +43,11 @@ def _frame800():
 # land a pixel elsewhere; the bounds below are what was measured plus slack, and the single-pass modes are recorded, not
 # hidden.
 FRAME_BOUNDS = {  # mode: (pixels > 2/255 allowed, PSNR floor in dB)
-    "fp32": (2, 100.0), "fp16x3": (2, 95.0), "mixed": (2, 80.0), "fp16": (300, 60.0), "bf16": (4000, 50.0)}  # measured: 0 / 0 / 0 / 100 / 1 673 pixels; 119 / 108 / 90 / 71 / 59 dB
+    "fp32": (2, 100.0), "fp16x3": (2, 95.0), "mixed": (2, 80.0), "fp16": (300, 60.0), "tf32": (300, 60.0),
+    "bf16": (4000, 50.0)}  # measured: 0 / 0 / 0 / 100 / (tf32: as fp16) / 1 673 pixels; 119 / 108 / 90 / 71 / 59 dB
 
 
-@pytest.mark.parametrize("prec", ["fp32", "fp16x3", "mixed", "fp16", "bf16"])
+@pytest.mark.parametrize("prec", ["fp32", "fp16x3", "mixed", "fp16", "tf32", "bf16"])
 def test_full_800_frame_against_the_oracle(renderer, cam, prec):
     want = _frame800()
     got = renderer.render_image(cam, 800, 800, 64, 128, precision=prec)

@@ -279,8 +279,9 @@ def test_weight_cache_file_is_deterministic_and_checked(tmp_path):
     version, n_nets = struct.unpack_from("<II", raw, 8)
     assert raw[:8] == b"NRFB200W" and n_nets == 2
     assert version >> 24 == 2 and version & 0xffffff != 0  # format revision | hash of the chunk-stream layout tag
-    # two nets x (f32 tensors + bf16 + fp16 + split-fp16 streams): 2 x (2 383 376 + 1 196 032 x 4) B + names / dims
-    assert 2 * (2383376 + 4 * 1196032) < len(raw) < 2 * (2383376 + 4 * 1196032) + 4096
+    # two nets x (f32 tensors + bf16 + fp16 + split-fp16 + tf32 streams): 2 x (2 383 376 + 1 196 032 x 4 + 2 375 680) B
+    # + names / dims
+    assert 2 * (2383376 + 4 * 1196032 + 2375680) < len(raw) < 2 * (2383376 + 4 * 1196032 + 2375680) + 4096
     w = np.fromfile(os.path.join(DATA, "fine", "dense5_kernel.bin"), np.float32)
     assert raw.count(w.tobytes()) == 1  # stored verbatim
     with pytest.raises(nb.NerfError) as e:
