@@ -17,7 +17,7 @@ grep "Function :" /tmp/_sass.txt | sed 's/.*Function : //' | c++filt | sed 's/(a
 echo
 echo "# ptxas -v (registers are the launch bound of 640 threads; setmaxnreg gives the epilogue warps 112, the control warps 32)"
 cd nerf_rs_b200/csrc
-for f in mlp_tc mlp_tc_x3 sampling; do
+for f in mlp_tc mlp_tc_x3 mlp_tc_tf32 sampling; do
   extra=""; [ $f = sampling ] && extra="-fmad=false"
   nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xcompiler -ffp-contract=off \
        -Xptxas -v $extra -c $f.cu -o /tmp/_$f.o 2>&1 | grep -E "Compiling entry|Used|spill" | sed 's/ptxas info    : //' | c++filt
