@@ -113,6 +113,46 @@ extern "C" {
         d_rgb: *mut f32,
         stream: *mut c_void,
     ) -> c_int;
+    /// Part `part` of the frame dealt out in stripes of `stripe_rays` pixel indices to `parts` renderers (stripe k
+    /// belongs to part k % parts) into the WHOLE host frame: what several GPUs driven from one process call, one
+    /// context and one thread each (rayon's role in the reference, lib.rs:533-550).
+    pub fn nerf_render_striped(
+        ctx: *mut NerfCtx,
+        cam: *const NerfCamera,
+        w: c_int,
+        h: c_int,
+        n_coarse: c_int,
+        n_fine: c_int,
+        precision: c_int,
+        smp: *const NerfSampling,
+        stripe_rays: i64,
+        parts: c_int,
+        part: c_int,
+        frame: *mut f32,
+    ) -> c_int;
+    /// integrate_ray (lib.rs:176-195) over host arrays: rgb [n_rays][n][3], sigma and t [n_rays][n], out [n_rays][3].
+    pub fn nerf_integrate_rays(
+        ctx: *mut NerfCtx,
+        rgb: *const f32,
+        sigma: *const f32,
+        t: *const f32,
+        n_rays: i64,
+        n: c_int,
+        far: f32,
+        out: *mut f32,
+    ) -> c_int;
+    /// The same without any device allocation (static 4 MiB device scratch; larger calls return NERF_E_UNSUPPORTED).
+    /// No counterpart in the reference.
+    pub fn nerf_integrate_rays_noalloc(
+        ctx: *mut NerfCtx,
+        rgb: *const f32,
+        sigma: *const f32,
+        t: *const f32,
+        n_rays: i64,
+        n: c_int,
+        far: f32,
+        out: *mut f32,
+    ) -> c_int;
     pub fn nerf_camera_from_json(path: *const c_char, out: *mut NerfCamera) -> c_int;
     pub fn nerf_save_ppm(path: *const c_char, w: c_int, h: c_int, rgb: *const f32) -> c_int;
 }
