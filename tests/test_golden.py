@@ -91,8 +91,8 @@ def test_gpu_800_band_against_the_oracle(renderer, cam):
     assert psnr >= 45.0 and mx > 2.0, ("fp16", mx, psnr)  # documented behaviour, see DESIGN.md 4.3
 
 
-def _frame800():
-    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "frame_800.npz"))
+def _frame800(name="frame_800.npz"):
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name))
     n = int(z["W"]) * int(z["H"])
     white = np.unpackbits(z["white"])[:n].astype(bool)
     frame = np.ones((n, 3), np.float32)
@@ -154,3 +154,16 @@ def test_gpu_orbit_bands_against_the_oracle(renderer):
             print(f"orbit pose {k} band vs oracle, {prec}: max {d.max() * 255:.3f}/255, pixels > 2/255: "
                   f"{int((d > 2 / 255).sum())}, PSNR {psnr:.1f} dB")
             assert int((d > 2.0 / 255.0).sum()) <= 2 and psnr >= psnr_min, (k, prec, float(d.max()) * 255, psnr)
+
+
+def test_oracle_reproduces_philox_frame_fixture(onets, ocam):
+    """Drift guard for tests/golden/frame_800_philox0.npz (make_frame800.py 6 philox 0): the oracle's whole 800x800
+    frame with the Philox jitter of the product's default sampling mode, seed 0."""
+    import hashlib
+    z, frame = _frame800("frame_800_philox0.npz")
+    assert int(z["seed"]) == 0 and hashlib.sha256(frame.tobytes()).hexdigest() == str(z["sha256"])
+    for row, col in ((150, 380), (450, 310)):
+        rb = row * 800 + col
+        rgb = O.render(onets[0], onets[1], ocam, 800, 800, 64, 128, mode=O.SAMPLING_PHILOX, seed=0, ray_begin=rb,
+                       ray_end=rb + 64)
+        assert np.abs(rgb - frame[rb:rb + 64]).max() <= 2e-6

@@ -27,9 +27,9 @@ def _psnr(a, b):
     return 10 * np.log10(1.0 / max(float(np.mean((a.astype(np.float64) - b) ** 2)), 1e-20))
 
 
-def _frame800():
-    """tests/golden/frame_800.npz (made by tests/golden/make_frame800.py): background mask + the other pixels."""
-    z = np.load(os.path.join(HERE, "golden", "frame_800.npz"))
+def _frame800(name="frame_800.npz"):
+    """tests/golden/frame_800*.npz (made by tests/golden/make_frame800.py): background mask + the other pixels."""
+    z = np.load(os.path.join(HERE, "golden", name))
     n = int(z["W"]) * int(z["H"])
     white = np.unpackbits(z["white"])[:n].astype(bool)
     frame = np.ones((n, 3), np.float32)
@@ -311,3 +311,18 @@ def test_fixed_size_importance_kernel_equals_the_generic_one(renderer, cam):
         want = np.stack([np.sort(np.concatenate([tt[i], O.sample_importance(tt[i], w[i], u[i])]), kind="stable")
                          for i in range(0, rays, 5)])
         assert np.abs(got[::5] - want).max() < 2e-6 and (np.diff(got, axis=1) >= 0).all()
+
+
+@pytest.mark.parametrize("prec", ["mixed", "fp32"])
+def test_full_800_frame_with_philox_jitter_against_the_oracle(renderer, cam, prec):
+    """The product default - Philox jitter seed 0 (CLI, C++ / Python / Rust mirrors), mixed precision - on all 640 000
+    pixels of the headline frame against the oracle with the same counter-based stream (frame_800_philox0.npz).  Jittered
+    samples take the unsorted paths of the sampler (sort + rank merge) at full size."""
+    want = _frame800("frame_800_philox0.npz")
+    got = renderer.render_image(cam, 800, 800, 64, 128, precision=prec, mode=nb.SAMPLING_PHILOX, seed=0)
+    d = np.abs(got - want).max(axis=1)
+    bad = int((d > 2.0 / 255.0).sum())
+    psnr = _psnr(got, want)
+    print(f"800x800 Philox frame vs oracle, {prec}: max {d.max() * 255:.3f}/255, pixels > 2/255: {bad} of {d.size}, "
+          f"> 1/255: {int((d > 1.0 / 255.0).sum())}, PSNR {psnr:.2f} dB")
+    assert np.isfinite(got).all() and bad <= 2 and psnr >= (95.0 if prec == "fp32" else 80.0), (prec, bad, psnr)
