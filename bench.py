@@ -309,6 +309,27 @@ def gpu_arm(args):
         step_device("fp16")
         fast_ms, _ = timed(lambda: step_device("fp16"), min(args.steps, 5), True)
         fast_ms /= min(args.steps, 5)
+    # Opt-in leg, reported beside the headline and never as it: NERF_OPT_SKIP_EMPTY_RAYS (include/nerf_b200.h) gives
+    # the rays without any coarse weight the background and skips their fine pass - NOT the reference's image.
+    opt_in = None
+    if world == 1 and args.precision == "mixed":
+        r.set_option(nb.OPT_SKIP_EMPTY_RAYS, 1)
+        try:
+            step_device()
+            k = min(args.steps, 5)
+            skip_ms, (s_mc, s_mf, s_sm, s_cp) = timed(step_device, k, True)
+            tm = r.timing()
+            torch.cuda.synchronize()
+            opt_in = {"ms_per_frame": skip_ms / k, "rays_per_s": n_rays / (skip_ms / k * 1e-3),
+                      "rays_skipped_fraction": tm["rays_skipped"] / max(tm["rays"], 1),
+                      "stage_ms": {"mlp_coarse": s_mc, "mlp_fine": s_mf, "sampling": s_sm, "composite": s_cp},
+                      "frame": frame.cpu().numpy().copy(),
+                      "note": "opt-in nerf_set_option(NERF_OPT_SKIP_EMPTY_RAYS): rays all of whose coarse weights are "
+                              "exactly 0 get the background without a fine pass; every other ray is bit-identical to "
+                              "the headline frame. Not the reference's pipeline, so never the headline value"}
+        finally:
+            r.set_option(nb.OPT_SKIP_EMPTY_RAYS, 0)
+        extra.update(head)
     step_e2e()
     e2e_ms, _ = timed(step_e2e, args.steps, False)
     # ---- parity, at every N: the frame the ranks assembled (through the device path and through the host API) against
@@ -338,6 +359,16 @@ def gpu_arm(args):
                 "pixels": int(d.size), "max_abs_diff_x255": float(d.max() * 255.0),
                 "pixels_over_2_255": int((d > 2.0 / 255.0).sum()), "pixels_over_1_255": int((d > 1.0 / 255.0).sum()),
                 "psnr_db": float(10.0 * np.log10(1.0 / max(float(np.mean((host_copy.astype(np.float64) - want) ** 2)), 1e-20)))})
+    if rank == 0 and opt_in is not None:
+        f = opt_in.pop("frame")
+        changed = (f != dev_frame).any(axis=1)
+        opt_in["pixels_differing_from_headline_frame"] = int(changed.sum())
+        opt_in["all_of_them_background"] = bool((f[changed] == 1.0).all())
+        if os.path.exists(gpath):
+            d = np.abs(f - want).max(axis=1)
+            opt_in["vs_oracle_reference_frame"] = {
+                "max_abs_diff_x255": float(d.max() * 255.0), "pixels_over_2_255": int((d > 2.0 / 255.0).sum()),
+                "psnr_db": float(10.0 * np.log10(1.0 / max(float(np.mean((f.astype(np.float64) - want) ** 2)), 1e-20)))}
     barrier()
     rgb8_ms = many_ms = None
     if world == 1:
@@ -398,6 +429,7 @@ def gpu_arm(args):
             "fp16_both_networks": None if fast_ms is None else {
                 "value": n_rays / (fast_ms * 1e-3), "unit": "rays/s", "ms_per_step": fast_ms,
                 "note": PRECISION_NOTE["fp16"] + "; same timing method as `value`"},
+            "opt_in_skip_empty_rays": opt_in,
             "e2e_rgb8": None if rgb8_ms is None else {
                 "value": n_rays / (rgb8_ms / max(args.steps // 2, 1) * 1e-3), "unit": "rays/s",
                 "d2h_bytes_per_step": n_rays * 3, "api": "nerf_render_rgb8 (device-side save_ppm quantiser)"},

@@ -126,7 +126,26 @@ typedef struct {
   float coarse_refine_ms;
   int64_t coarse_samples;
   int64_t coarse_refined;
+  /* rays the render covered, and how many of them NERF_OPT_SKIP_EMPTY_RAYS finished without a fine pass (0 unless set) */
+  int64_t rays;
+  int64_t rays_skipped;
 } nerf_timing;
+
+/* Options of a context (nerf_set_option).  All default to the reference's behaviour. */
+typedef enum {
+  /* Opt-in, NOT the reference's image (the reference has no counterpart: lib.rs:353-472 runs
+   * the fine network on every ray).  A ray ALL of whose coarse weights (compute_weights, lib.rs:250-283) are exactly 0
+   * gets integrate_ray's value for a ray without weight - rgb (1,1,1), depth 0, opacity 0 (lib.rs:194) - and its fine
+   * pass is not run; every other ray is computed exactly as without the option, bit for bit.  The image differs from
+   * the reference's only where the fine network finds density on a ray the coarse network sees as empty.  On the lego
+   * frame 35 % of the rays are skipped and the frame takes 92 ms instead of 124 (29 pixels of 640 000 move by more than
+   * 2/255 from the oracle's frame, 79.9 dB).  The other background rays cannot be told from the coarse pass: the coarse
+   * network puts a haze of more than 3 % opacity on them, which only the fine network clears (a threshold on the
+   * coarse opacity was measured and skips next to nothing more up to 30 000 ppm, profiles/r02_skip_rays_thresholds.json, and was not kept).  A render in this mode synchronises its
+   * stream once per chunk of rays (the size of the fine pass comes back to the host), so the *_device entry points are
+   * not fully asynchronous while it is set; nerf_render_stages ignores it. */
+  NERF_OPT_SKIP_EMPTY_RAYS = 1
+} nerf_option;
 
 const char* nerf_last_error(void);
 const char* nerf_version(void);
@@ -250,6 +269,11 @@ int nerf_integrate_rays_noalloc(nerf_ctx*, const float* rgb, const float* sigma,
                                 float far_, float* out /*[n_rays][3]*/);
 
 int nerf_get_timing(nerf_ctx*, nerf_timing* out);
+
+/* Context options (nerf_option).  Unknown options: NERF_E_ARG.  Also settable at creation through the environment
+ * (NERF_B200_SKIP_EMPTY_RAYS=1). */
+int nerf_set_option(nerf_ctx*, int option, int value);
+int nerf_get_option(nerf_ctx*, int option, int* value);
 
 /* Host-side helpers of the boundary (no GPU needed). */
 /* camera_from_samples (lib.rs:614-645) over the JSON keys near, far, camera_origin, camera_forward,

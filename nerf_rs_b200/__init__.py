@@ -35,7 +35,9 @@ EXPORTS = ["nerf_last_error", "nerf_version", "nerf_create", "nerf_create_from_t
            "nerf_quantize_rgb8_gpu", "nerf_render_aux", "nerf_render_aux_device", "nerf_build_weight_cache",
            "nerf_create_from_cache", "nerf_shared_frame_create", "nerf_shared_frame_open", "nerf_shared_frame_close",
            "nerf_shared_frame_create_fd", "nerf_shared_frame_open_fd", "nerf_shared_frame_close_fd",
-           "nerf_render_striped", "nerf_render_striped_device", "nerf_integrate_rays_noalloc"]
+           "nerf_render_striped", "nerf_render_striped_device", "nerf_integrate_rays_noalloc", "nerf_set_option",
+           "nerf_get_option"]
+OPT_SKIP_EMPTY_RAYS = 1  # nerf_option (include/nerf_b200.h)
 NOALLOC_MAX_BYTES = 4 << 20  # NERF_NOALLOC_MAX_BYTES (include/nerf_b200.h)
 
 
@@ -65,7 +67,8 @@ class Stages(C.Structure):
 class Timing(C.Structure):
     _fields_ = [("total_ms", C.c_float), ("mlp_coarse_ms", C.c_float), ("mlp_fine_ms", C.c_float),
                 ("sampling_ms", C.c_float), ("composite_ms", C.c_float), ("kernel_launches", C.c_int32),
-                ("coarse_refine_ms", C.c_float), ("coarse_samples", C.c_int64), ("coarse_refined", C.c_int64)]
+                ("coarse_refine_ms", C.c_float), ("coarse_samples", C.c_int64), ("coarse_refined", C.c_int64),
+                ("rays", C.c_int64), ("rays_skipped", C.c_int64)]
 
 
 class Tensor(C.Structure):
@@ -127,6 +130,8 @@ def lib():
     L.nerf_integrate_rays.argtypes = [vp, _f32p, _f32p, _f32p, i64, i32, C.c_float, _f32p]
     L.nerf_integrate_rays_noalloc.argtypes = [vp, _f32p, _f32p, _f32p, i64, i32, C.c_float, _f32p]
     L.nerf_get_timing.argtypes = [vp, C.POINTER(Timing)]
+    L.nerf_set_option.argtypes = [vp, i32, i32]
+    L.nerf_get_option.argtypes = [vp, i32, C.POINTER(i32)]
     L.nerf_camera_from_json.argtypes = [C.c_char_p, C.POINTER(Camera)]
     d3 = C.POINTER(C.c_double)
     L.nerf_camera_from_values.argtypes = [C.c_double, C.c_double, d3, d3, d3, d3, C.POINTER(Camera)]

@@ -89,6 +89,13 @@ struct nerf_ctx {
   // NERF_B200_SELECT_MARGIN: bound on the fp16 pass's pre-activation error near zero.  Measured (scripts/select_check.py,
   // 800x800 reference pose): the frame stays bit-identical down to 0.03, so 0.5 keeps a factor 16.
   float select_margin = 0.5f;
+  // nerf_set_option(NERF_OPT_SKIP_EMPTY_RAYS) / NERF_B200_SKIP_EMPTY_RAYS=1 (opt-in, NOT the reference's image; DESIGN.md
+  // 4.6): rays without any coarse weight get the background and skip the fine pass.  The number of surviving rays comes
+  // back through a pinned word, so a render in this mode synchronises its stream once per chunk.
+  bool skip_empty_rays = false;
+  DevBuf ray_list, ray_count, dirs_alive;
+  uint32_t* h_ray_count = nullptr;
+  int64_t rays_total = 0, rays_skipped = 0;  // since timing_start
   float select_tau = 12.0f;     // NERF_B200_SELECT_TAU: optical depth behind which no coarse weight survives (T < 6e-6)
   // 8-bit output path: two device frames + two pinned host frames so that the copy of one view overlaps the next render
   DevBuf q8[2], depth, acc;
@@ -206,6 +213,7 @@ int create_common(const TensorMap& coarse, const TensorMap& fine, int device, ne
   }
   if (const char* e = std::getenv("NERF_B200_COARSE_SELECT")) ctx->coarse_select = std::atoi(e) != 0;
   if (const char* e = std::getenv("NERF_B200_SKIP_EMPTY")) ctx->skip_empty = std::atoi(e) != 0;
+  if (const char* e = std::getenv("NERF_B200_SKIP_EMPTY_RAYS")) ctx->skip_empty_rays = std::atoi(e) != 0;
   if (const char* e = std::getenv("NERF_B200_COARSE_STAGES")) ctx->coarse_stages = std::max(1, std::atoi(e));
   if (const char* e = std::getenv("NERF_B200_SELECT_MARGIN")) ctx->select_margin = (float)std::atof(e);
   if (const char* e = std::getenv("NERF_B200_SELECT_TAU")) ctx->select_tau = (float)std::atof(e);
@@ -432,15 +440,40 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
       if (rc) return rc;
     }
 
+    // Skip-empty-rays mode: the rays the coarse pass gives no weight are finished here (background); the fine pass runs
+    // over the compacted list of the others.  Not taken for stage dumps, whose arrays are indexed by ray.
+    int64_t nr = n;                     // rays of the fine pass
+    const int32_t* ray_ids = nullptr;   // their ray numbers within the chunk (null: all, in order)
+    if (c->skip_empty_rays && !want_wc) {
+      if ((rc = c->ray_list.reserve(n * 4)) || (rc = c->ray_count.reserve(256)) || (rc = c->dirs_alive.reserve(n * 3 * 4)))
+        return rc;
+      if (c->h_ray_count == nullptr) NERF_CUDA(cudaMallocHost(reinterpret_cast<void**>(&c->h_ray_count), 64));
+      span_begin(c, ST_SAMPLING, s);
+      NERF_CUDA(cudaMemsetAsync(c->ray_count.p, 0, 4, s));
+      NERF_CUDA(launch_ray_pick(c->sigc.as<float>(), c->tc.as<float>(), c->dirs.as<float>(), n, nc, cam.far_, omap,
+                                c->ray_list.as<int32_t>(), c->ray_count.as<uint32_t>(), c->dirs_alive.as<float>(), d_rgb,
+                                d_depth, d_acc, s));
+      NERF_CUDA(cudaMemcpyAsync(c->h_ray_count, c->ray_count.p, 4, cudaMemcpyDeviceToHost, s));
+      span_end(c, s);
+      ++c->launches;
+      NERF_CUDA(cudaStreamSynchronize(s));
+      nr = (int64_t)*c->h_ray_count;
+      ray_ids = c->ray_list.as<int32_t>();
+      src.dirs = c->dirs_alive.as<float>();
+      c->rays_skipped += n - nr;
+    }
+    c->rays_total += n;
+    if (nr == 0) continue;
+
     span_begin(c, ST_SAMPLING, s);
     NERF_CUDA(launch_importance(c->tc.as<float>(), c->sigc.as<float>(), nullptr, nc, nf, cam.far_, mode, seed,
-                                d_u ? d_u + off * nf : nullptr, map, n, c->tf.as<float>(),
-                                want_wc ? c->wc.as<float>() : nullptr, s));
+                                d_u ? d_u + off * nf : nullptr, map, nr, c->tf.as<float>(),
+                                want_wc ? c->wc.as<float>() : nullptr, s, ray_ids));
     span_end(c, s);
     ++c->launches;
 
     src.S = nm;
-    src.B = n * nm;
+    src.B = nr * nm;
     src.t = c->tf.as<float>();
     dst = SampleDst{c->sigf.as<float>(), c->rgbf.as<float>(), 0.0f, c->skip_empty ? 1 : 0};
     span_begin(c, ST_MLP_FINE, s);
@@ -449,8 +482,8 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
     if (rc) return rc;
 
     span_begin(c, ST_COMPOSITE, s);
-    NERF_CUDA(launch_composite(c->rgbf.as<float>(), c->sigf.as<float>(), c->tf.as<float>(), n, nm, cam.far_, omap, d_rgb,
-                               d_depth, d_acc, s));
+    NERF_CUDA(launch_composite(c->rgbf.as<float>(), c->sigf.as<float>(), c->tf.as<float>(), nr, nm, cam.far_, omap, d_rgb,
+                               d_depth, d_acc, s, ray_ids));
     span_end(c, s);
     ++c->launches;
   }
@@ -467,6 +500,7 @@ void timing_start(nerf_ctx* c, cudaStream_t s) {
   c->launches = 0;
   c->refine_total = 0;
   c->refine_pending = false;
+  c->rays_total = c->rays_skipped = 0;
   if (c->sel_count.p) cudaMemsetAsync(c->sel_count.p, 0, 8, s);  // [0] list length of the chunk, [1] running total
   c->have_timing = true;
   cudaEventRecord(c->ev_begin, s);
@@ -667,8 +701,10 @@ void nerf_destroy(nerf_ctx* c) {
       c->vmm_frames.clear();
     }
     for (DevBuf* b : {&c->dirs, &c->tc, &c->sigc, &c->wc, &c->tf, &c->sigf, &c->rgbf, &c->out, &c->in_a, &c->in_b,
-                      &c->jit, &c->uni, &c->q8[0], &c->q8[1], &c->depth, &c->acc, &c->sel_list, &c->sel_count, &c->alive[0], &c->alive[1]})
+                      &c->jit, &c->uni, &c->q8[0], &c->q8[1], &c->depth, &c->acc, &c->sel_list, &c->sel_count, &c->alive[0], &c->alive[1],
+                      &c->ray_list, &c->ray_count, &c->dirs_alive})
       b->release();
+    if (c->h_ray_count) cudaFreeHost(c->h_ray_count);
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
     for (int i = 0; i < 2; ++i) {
       if (c->pinned[i]) cudaFreeHost(c->pinned[i]);
@@ -798,12 +834,15 @@ static int render_host(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc
   const bool saved_skip = c->skip_empty;
   if (want_stages) c->chunk_rays = n;  // stage dumps read the workspaces of a single chunk
   if (want_stages && st->rgb_f) c->skip_empty = false;  // a caller who asks for every sample's colour gets it
+  const bool saved_skip_rays = c->skip_empty_rays;
+  if (want_stages) c->skip_empty_rays = false;  // stage arrays are indexed by ray: every ray takes the whole pipeline
   timing_start(c, s);
   rc = render_range(c, *cam, W, H, nc, nf, precision, mode, smp ? smp->seed : 0, d_jit, d_u, rb, re,
                     c->out.as<float>(), want_stages && st->w_c, s);
   timing_stop(c, s);
   c->chunk_rays = saved_chunk;
   c->skip_empty = saved_skip;
+  c->skip_empty_rays = saved_skip_rays;
   if (rc != NERF_OK) return rc;
   NERF_CUDA(cudaMemcpyAsync(rgb, c->out.p, n * 12, cudaMemcpyDeviceToHost, s));
   if (want_stages) {
@@ -1331,6 +1370,38 @@ int nerf_shared_frame_close_fd(nerf_ctx* c, void* d_ptr) {
   return NERF_OK;
 }
 
+int nerf_set_option(nerf_ctx* c, int option, int value) {
+  if (!c) {
+    set_error("nerf_set_option: null context");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  switch (option) {
+    case NERF_OPT_SKIP_EMPTY_RAYS:
+      c->skip_empty_rays = value != 0;
+      return NERF_OK;
+    default:
+      set_error("nerf_set_option: unknown option " + std::to_string(option));
+      return NERF_E_ARG;
+  }
+}
+
+int nerf_get_option(nerf_ctx* c, int option, int* value) {
+  if (!c || !value) {
+    set_error("nerf_get_option: null argument");
+    return NERF_E_ARG;
+  }
+  std::lock_guard<std::recursive_mutex> lk(c->mu);
+  switch (option) {
+    case NERF_OPT_SKIP_EMPTY_RAYS:
+      *value = c->skip_empty_rays ? 1 : 0;
+      return NERF_OK;
+    default:
+      set_error("nerf_get_option: unknown option " + std::to_string(option));
+      return NERF_E_ARG;
+  }
+}
+
 int nerf_get_timing(nerf_ctx* c, nerf_timing* out) {
   if (!c || !out) {
     set_error("nerf_get_timing: null argument");
@@ -1358,6 +1429,8 @@ int nerf_get_timing(nerf_ctx* c, nerf_timing* out) {
   }
   out->kernel_launches = c->launches;
   out->coarse_samples = c->refine_total;
+  out->rays = c->rays_total;
+  out->rays_skipped = c->rays_skipped;
   if (c->refine_pending) {  // ev_end has completed, so the counters are final
     uint32_t cnt[2] = {0, 0};
     NERF_CUDA(cudaMemcpy(cnt, c->sel_count.p, sizeof(cnt), cudaMemcpyDeviceToHost));

@@ -132,7 +132,9 @@ cudaError_t launch_ray_dirs(const RayBasis& rb, int64_t ray_begin, int64_t n_ray
 cudaError_t launch_importance(const float* d_tc, const float* d_sigc, const float* d_w_in, int nc, int nf, float far_,
                               int mode,
                               uint64_t seed, const float* d_u, RayMap map, int64_t n_rays, float* d_tf,
-                              float* d_wc_or_null, cudaStream_t s);
+                              float* d_wc_or_null, cudaStream_t s, const int32_t* d_ray_ids = nullptr);
+// d_ray_ids (nullable, skip-empty-rays mode): launch slot i works on ray d_ray_ids[i] - the coarse inputs, the
+// uniforms, the Philox key and d_wc are indexed by ray, the merged samples d_tf by slot.
 // Two-pass coarse densities: d_sig holds the single-pass fp16 pre-activations on entry and
 // relu(pre-activation) on return; the ids of the samples whose density can reach the coarse weights are appended to
 // d_list, their number to *d_count (zeroed by the caller).
@@ -149,6 +151,13 @@ cudaError_t launch_quantize(const float* d_rgb, int64_t n_pixels, int channels, 
 // ray r's outputs go to element omap.pixel(r) of d_out / d_depth / d_acc
 cudaError_t launch_composite(const float* d_rgb, const float* d_sigma, const float* d_t, int64_t n_rays, int n,
                              float far_, RayMap omap, float* d_out, float* d_depth /*nullable*/, float* d_acc /*nullable*/,
-                             cudaStream_t s);
+                             cudaStream_t s, const int32_t* d_ray_ids = nullptr);
+// d_ray_ids (nullable): the inputs are indexed by launch slot i and the outputs go to omap.pixel(d_ray_ids[i]).
+// Skip-empty-rays mode (opt-in, not the reference's image): rays all of whose coarse weights are exactly
+// zero get the background (rgb 1, depth 0, opacity 0) at omap.pixel(ray) straight away; the others are appended to
+// d_list (their number to *d_count, zeroed by the caller) and their directions copied to d_dirs_out in list order.
+cudaError_t launch_ray_pick(const float* d_sigc, const float* d_tc, const float* d_dirs, int64_t n_rays, int nc,
+                            float far_, RayMap omap, int32_t* d_list, uint32_t* d_count, float* d_dirs_out, float* d_out,
+                            float* d_depth /*nullable*/, float* d_acc /*nullable*/, cudaStream_t s);
 
 }  // namespace nerf

@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) importance_kernel(
     const float* __restrict__ tc, const float* __restrict__ sigc, const float* __restrict__ w_in, int nc, int nf,
     float far_, int mode, uint64_t seed,
     const float* __restrict__ u_in, RayMap map, int64_t n_rays, float* __restrict__ tf,
-    float* __restrict__ wc_out) {
+    float* __restrict__ wc_out, const int32_t* __restrict__ ray_ids) {
   extern __shared__ float smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nm = nc + nf;
@@ -175,7 +175,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) importance_kernel(
   float* s_c = s_f + pf;      // sorted copy of the coarse samples (only used when they arrive unsorted)
   const int m = nc - 2;  // pdf_weights = weights[1..n-1] (lib.rs:299)
 
-  for (int64_t ray = blockIdx.x * (int64_t)kWarpsPerCta + warp; ray < n_rays; ray += (int64_t)gridDim.x * kWarpsPerCta) {
+  for (int64_t slot = blockIdx.x * (int64_t)kWarpsPerCta + warp; slot < n_rays;
+       slot += (int64_t)gridDim.x * kWarpsPerCta) {
+    const int64_t ray = ray_ids != nullptr ? (int64_t)ray_ids[slot] : slot;  // inputs by ray, samples out by slot
     const float* tr = tc + ray * nc;
     const float* sr = sigc + ray * nc;
     for (int i = lane; i < nc; i += 32) s_t[i] = tr[i];
@@ -193,7 +195,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) importance_kernel(
       }
     }
     __syncwarp();
-    float* out = tf + ray * nm;
+    float* out = tf + slot * nm;
     if (nf > 0) {
       for (int i = lane; i < m; i += 32) s_pdf[i] = fmaxf(s_w[i + 1], 0.0f) + 1e-5f;  // lib.rs:309
       for (int i = lane; i < nc - 1; i += 32) s_bins[i] = 0.5f * (s_t[i] + s_t[i + 1]);  // lib.rs:286
@@ -300,7 +302,7 @@ template <int NC, int NF>
 __global__ void __launch_bounds__(kWarpsPerCta * 32) importance_fixed_kernel(
     const float* __restrict__ tc, const float* __restrict__ sigc, const float* __restrict__ w_in, float far_, int mode,
     uint64_t seed, const float* __restrict__ u_in, RayMap map, int64_t n_rays, float* __restrict__ tf,
-    float* __restrict__ wc_out) {
+    float* __restrict__ wc_out, const int32_t* __restrict__ ray_ids) {
   static_assert(NC % 32 == 0 && NF % 32 == 0 && (NC & (NC - 1)) == 0 && (NF & (NF - 1)) == 0, "power-of-two sample counts");
   constexpr int M = NC - 2, NM = NC + NF;  // pdf_weights = weights[1..n-1] (lib.rs:299)
   constexpr int kPerWarp = 5 * NC + NF + NM;
@@ -314,7 +316,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) importance_fixed_kernel(
   float* s_f = s_bins + NC;
   int* s_mark = reinterpret_cast<int*>(s_f + NF);
 
-  for (int64_t ray = blockIdx.x * (int64_t)kWarpsPerCta + warp; ray < n_rays; ray += (int64_t)gridDim.x * kWarpsPerCta) {
+  for (int64_t slot = blockIdx.x * (int64_t)kWarpsPerCta + warp; slot < n_rays;
+       slot += (int64_t)gridDim.x * kWarpsPerCta) {
+    const int64_t ray = ray_ids != nullptr ? (int64_t)ray_ids[slot] : slot;  // inputs by ray, samples out by slot
     const float* tr = tc + ray * NC;
 #pragma unroll
     for (int i = lane; i < NC; i += 32) s_t[i] = tr[i];
@@ -406,7 +410,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) importance_fixed_kernel(
 #pragma unroll
     for (int r = 0; r < NF / 32; ++r) s_f[lane + 32 * r] = vals[r];
     __syncwarp();
-    float* out = tf + ray * NM;
+    float* out = tf + slot * NM;
     const bool fine_sorted = warp_is_sorted(s_f, NF, lane), coarse_sorted = warp_is_sorted(s_t, NC, lane);
     if (fine_sorted && coarse_sorted) {
 #pragma unroll
@@ -598,6 +602,61 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) coarse_alive_kernel(const f
   }
 }
 
+// Skip-empty-rays mode (opt-in): which rays does the coarse pass give any weight at all?  One warp per
+// ray evaluates compute_weights (lib.rs:250-283) exactly as K3 will; a ray whose weights are all exactly 0 is written
+// out as background here and never reaches the fine pass, the others are appended to `list` (one reservation per CTA
+// of 8 rays) with their directions.  NaN weights keep the ray.
+__global__ void __launch_bounds__(kWarpsPerCta * 32) ray_pick_kernel(const float* __restrict__ sig,
+                                                                     const float* __restrict__ t,
+                                                                     const float* __restrict__ dirs, int64_t n_rays,
+                                                                     int nc, float far_, RayMap omap,
+                                                                     int32_t* __restrict__ list,
+                                                                     uint32_t* __restrict__ count,
+                                                                     float* __restrict__ dirs_out,
+                                                                     float* __restrict__ out,
+                                                                     float* __restrict__ depth_out,
+                                                                     float* __restrict__ acc_out) {
+  __shared__ uint32_t s_alive[kWarpsPerCta], s_base;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int64_t r0 = blockIdx.x * (int64_t)kWarpsPerCta; r0 < n_rays; r0 += (int64_t)gridDim.x * kWarpsPerCta) {
+    const int64_t ray = r0 + warp;
+    bool alive = false;
+    if (ray < n_rays) {
+      float carry = 1.0f;
+      bool any = false;
+      for (int base = 0; base < nc; base += 32) {
+        const float w = warp_weights_round(sig + ray * nc, t + ray * nc, nc, far_, base, lane, carry);
+        any = any || !(w == 0.0f);
+      }
+      alive = __any_sync(kFull, any);
+      if (!alive) {
+        const int64_t opix = omap.pixel(ray);
+        if (lane < 3) out[opix * 3 + lane] = 1.0f;  // integrate_ray with no weight: 0 + (1 - 0) * white (lib.rs:194)
+        if (lane == 0 && depth_out != nullptr) depth_out[opix] = 0.0f;
+        if (lane == 0 && acc_out != nullptr) acc_out[opix] = 0.0f;
+      }
+    }
+    if (lane == 0) s_alive[warp] = alive ? 1u : 0u;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t sum = 0;
+      for (int w = 0; w < kWarpsPerCta; ++w) {
+        const uint32_t a = s_alive[w];
+        s_alive[w] = sum;
+        sum += a;
+      }
+      s_base = sum ? atomicAdd(count, sum) : 0u;
+    }
+    __syncthreads();
+    if (alive) {
+      const uint32_t pos = s_base + s_alive[warp];
+      if (lane == 0) list[pos] = (int32_t)ray;
+      if (lane < 3) dirs_out[(int64_t)pos * 3 + lane] = dirs[ray * 3 + lane];
+    }
+    __syncthreads();
+  }
+}
+
 // compute_weights alone (stage parity entry point).
 __global__ void __launch_bounds__(kWarpsPerCta * 32) weights_kernel(const float* __restrict__ sigma,
                                                                     const float* __restrict__ t, int64_t n_rays,
@@ -623,7 +682,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) composite_kernel(const floa
                                                                       int n, float far_, RayMap omap, bool staged,
                                                                       float* __restrict__ out,
                                                                       float* __restrict__ depth_out,
-                                                                      float* __restrict__ acc_out) {
+                                                                      float* __restrict__ acc_out,
+                                                                      const int32_t* __restrict__ ray_ids) {
   extern __shared__ float4 s_stage[];  // staged launches: one ray's colours per warp, [n * 3] floats
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // A ray's colours are n * 3 consecutive floats; read lane by lane that is three 4-byte loads at a 12-byte stride.
@@ -717,7 +777,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) composite_kernel(const floa
       depth += __shfl_xor_sync(kFull, depth, d);
     }
     // optional outputs the reference does not have: depth = sum w_i t_i, accumulated opacity = sum w_i
-    const int64_t opix = omap.pixel(ray);
+    const int64_t opix = omap.pixel(ray_ids != nullptr ? (int64_t)ray_ids[ray] : ray);  // inputs by slot, pixel by ray
     if (lane == 0 && depth_out != nullptr) depth_out[opix] = depth;
     if (lane == 0 && acc_out != nullptr) acc_out[opix] = acc;
     if (n == 0) { r = g = b = 0.0f; acc = 1.0f; }  // lib.rs:178-180: no samples -> black
@@ -762,7 +822,7 @@ cudaError_t launch_ray_dirs(const RayBasis& rb, int64_t ray_begin, int64_t n_ray
 
 cudaError_t launch_importance(const float* d_tc, const float* d_sigc, const float* d_w_in, int nc, int nf, float far_,
                               int mode, uint64_t seed, const float* d_u, RayMap map, int64_t n_rays, float* d_tf,
-                              float* d_wc, cudaStream_t s) {
+                              float* d_wc, cudaStream_t s, const int32_t* d_ray_ids) {
   if (n_rays == 0) return cudaSuccess;
   // the reference's sample counts have a kernel of their own (NERF_B200_GENERIC_IMPORTANCE=1 forces the generic one:
   // the two must agree bit for bit, tests/test_gpu_round2.py)
@@ -770,13 +830,13 @@ cudaError_t launch_importance(const float* d_tc, const float* d_sigc, const floa
   if (nc == 64 && nf == 128 && !(force != nullptr && force[0] == '1')) {
     constexpr size_t kFixedSmem = (size_t)kWarpsPerCta * (5 * 64 + 128 + 192) * sizeof(float);  // 20 KiB
     importance_fixed_kernel<64, 128><<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, kFixedSmem, s>>>(
-        d_tc, d_sigc, d_w_in, far_, mode, seed, d_u, map, n_rays, d_tf, d_wc);
+        d_tc, d_sigc, d_w_in, far_, mode, seed, d_u, map, n_rays, d_tf, d_wc, d_ray_ids);
     return cudaGetLastError();
   }
   const size_t smem = importance_smem_bytes(nc, nf);
   if (smem > kImportanceMaxSmem) return cudaErrorInvalidValue;
   importance_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, smem, s>>>(
-      d_tc, d_sigc, d_w_in, nc, nf, far_, mode, seed, d_u, map, n_rays, d_tf, d_wc);
+      d_tc, d_sigc, d_w_in, nc, nf, far_, mode, seed, d_u, map, n_rays, d_tf, d_wc, d_ray_ids);
   return cudaGetLastError();
 }
 
@@ -794,6 +854,15 @@ cudaError_t launch_coarse_alive(const float* d_sig, const float* d_t, int64_t n_
   if (n_rays == 0) return cudaSuccess;
   coarse_alive_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, 0, s>>>(
       d_sig, d_t, n_rays, nc, s_end, far_, tau_cut, d_in_list, d_in_count, d_list, d_count);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_ray_pick(const float* d_sigc, const float* d_tc, const float* d_dirs, int64_t n_rays, int nc,
+                            float far_, RayMap omap, int32_t* d_list, uint32_t* d_count, float* d_dirs_out, float* d_out,
+                            float* d_depth, float* d_acc, cudaStream_t s) {
+  if (n_rays == 0) return cudaSuccess;
+  ray_pick_kernel<<<grid_for(n_rays, kWarpsPerCta), kWarpsPerCta * 32, 0, s>>>(
+      d_sigc, d_tc, d_dirs, n_rays, nc, far_, omap, d_list, d_count, d_dirs_out, d_out, d_depth, d_acc);
   return cudaGetLastError();
 }
 
@@ -831,14 +900,16 @@ cudaError_t launch_quantize(const float* d_rgb, int64_t n_pixels, int channels, 
 }
 
 cudaError_t launch_composite(const float* d_rgb, const float* d_sigma, const float* d_t, int64_t n_rays, int n,
-                             float far_, RayMap omap, float* d_out, float* d_depth, float* d_acc, cudaStream_t s) {
+                             float far_, RayMap omap, float* d_out, float* d_depth, float* d_acc, cudaStream_t s,
+                             const int32_t* d_ray_ids) {
   if (n_rays == 0) return cudaSuccess;
   const size_t stage = (size_t)kWarpsPerCta * n * 3 * sizeof(float);
   const bool staged = n > 0 && (n * 3) % 4 == 0 && stage <= 48 * 1024 && (reinterpret_cast<uintptr_t>(d_rgb) & 15u) == 0;
   const int grid = grid_for(n_rays, kWarpsPerCta), threads = kWarpsPerCta * 32;
   const size_t smem = staged ? stage : 0;
 #define NERF_COMPOSITE(R) \
-  composite_kernel<R><<<grid, threads, smem, s>>>(d_rgb, d_sigma, d_t, n_rays, n, far_, omap, staged, d_out, d_depth, d_acc)
+  composite_kernel<R><<<grid, threads, smem, s>>>(d_rgb, d_sigma, d_t, n_rays, n, far_, omap, staged, d_out, d_depth, d_acc, \
+                                                  d_ray_ids)
   if (n <= 64) NERF_COMPOSITE(2);
   else if (n <= 128) NERF_COMPOSITE(4);
   else if (n <= 192) NERF_COMPOSITE(6);  // the reference's 64 + 128 samples

@@ -218,6 +218,15 @@ class Renderer:
         _check(lib().nerf_integrate_rays(self._h, _p(rgb), _p(sigma), _p(t), t.shape[0], t.shape[1], far, _p(out)))
         return out
 
+    def set_option(self, option, value):
+        """nerf_set_option: e.g. (nerf_rs_b200.OPT_SKIP_EMPTY_RAYS, 1) - opt-in, not the reference's image."""
+        _check(lib().nerf_set_option(self._h, int(option), int(value)))
+
+    def get_option(self, option):
+        v = C.c_int32(0)
+        _check(lib().nerf_get_option(self._h, int(option), C.byref(v)))
+        return v.value
+
     def timing(self):
         t = Timing()
         _check(lib().nerf_get_timing(self._h, C.byref(t)))

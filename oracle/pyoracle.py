@@ -215,6 +215,18 @@ def render(coarse, fine, cam, W, H, nc, nf, mode=SAMPLING_DET, seed=0, jitter=No
     return (rgb, dump) if stages else rgb
 
 
+def render_skip_empty_rays(coarse, fine, cam, W, H, nc, nf, **kw):
+    """Definition of the product's opt-in NERF_OPT_SKIP_EMPTY_RAYS (include/nerf_b200.h; the reference has no such
+    mode): render_image as above, except that a ray ALL of whose coarse weights (compute_weights, src/lib.rs:250-283)
+    are exactly 0 takes integrate_ray's value for a ray without weight, 0 + (1 - 0) * white (src/lib.rs:194), instead
+    of the fine pass's.  Returns (rgb [n,3], skipped [n] bool)."""
+    rgb, st = render(coarse, fine, cam, W, H, nc, nf, stages=True, **kw)
+    skipped = np.all(st["w_c"] == 0.0, axis=1)
+    rgb = rgb.copy()
+    rgb[skipped] = 1.0
+    return rgb, skipped
+
+
 def save_ppm(path, W, H, rgb):
     rgb = _f32(rgb)
     assert rgb.size == W * H * 3

@@ -45,6 +45,7 @@ pub const PREC_FP16: c_int = 2;
 pub const PREC_TF32: c_int = 3;
 pub const PREC_FP16X3: c_int = 4;
 pub const PREC_MIXED: c_int = 5;
+pub const OPT_SKIP_EMPTY_RAYS: c_int = 1;
 pub const NET_COARSE: c_int = 0;
 pub const NET_FINE: c_int = 1;
 
@@ -153,6 +154,10 @@ extern "C" {
         far: f32,
         out: *mut f32,
     ) -> c_int;
+    /// Context options (nerf_option).  OPT_SKIP_EMPTY_RAYS is opt-in and NOT the reference's image: rays without any
+    /// coarse weight get the background and skip the fine pass (include/nerf_b200.h).
+    pub fn nerf_set_option(ctx: *mut NerfCtx, option: c_int, value: c_int) -> c_int;
+    pub fn nerf_get_option(ctx: *mut NerfCtx, option: c_int, value: *mut c_int) -> c_int;
     pub fn nerf_camera_from_json(path: *const c_char, out: *mut NerfCamera) -> c_int;
     pub fn nerf_save_ppm(path: *const c_char, w: c_int, h: c_int, rgb: *const f32) -> c_int;
 }
