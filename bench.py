@@ -49,8 +49,8 @@ PRECISION_NOTE = {
 }
 # dram__bytes_read.sum + dram__bytes_write.sum of the fine-pass launch, 800x800 c64+f128: a CONSTANT copied from one
 # `ncu --set full` capture (file below), not measured by this run
-NCU_FINE_DRAM_GB = 0.520 + 1.914
-NCU_FINE_DRAM_SOURCE = "profiles/r01_mlp_tc_v15_ncu_full_summary.csv"
+NCU_FINE_DRAM_GB = 0.518 + 1.915  # mlp_tc_kernel<1,0,1>, the fine pass of the reference frame
+NCU_FINE_DRAM_SOURCE = "profiles/r02_frame_ncu_full_summary.csv"
 
 
 def load_peaks():
