@@ -17,7 +17,7 @@ import pytest
 from oracle import pyoracle as O
 import nerf_rs_b200 as nb
 
-from .conftest import DATA
+from .conftest import CAM_JSON as CAM, DATA
 
 pytestmark = pytest.mark.gpu
 HERE = os.path.dirname(os.path.abspath(__file__))
@@ -326,3 +326,24 @@ def test_full_800_frame_with_philox_jitter_against_the_oracle(renderer, cam, pre
     print(f"800x800 Philox frame vs oracle, {prec}: max {d.max() * 255:.3f}/255, pixels > 2/255: {bad} of {d.size}, "
           f"> 1/255: {int((d > 1.0 / 255.0).sum())}, PSNR {psnr:.2f} dB")
     assert np.isfinite(got).all() and bad <= 2 and psnr >= (95.0 if prec == "fp32" else 80.0), (prec, bad, psnr)
+
+
+def test_stratified_samples_bit_exact_for_every_count_and_mode(renderer, cam):
+    """K1 has a kernel for sample counts that are a multiple of four (four samples per thread, one Philox block, one
+    128-bit store) and the per-sample kernel for the others: both against the oracle's stratified_samples
+    (src/lib.rs:233-248) and Philox stream, bit for bit, on a ray range that does not start at pixel 0."""
+    W, H = 16, 8
+    b, e = 5, 117
+    n = e - b
+    rng = np.random.default_rng(77)
+    for nc in (64, 12, 4, 10, 7, 3):
+        jit = rng.uniform(0, 1, (n, nc)).astype(np.float32)
+        u = rng.uniform(0, 1, (n, 4)).astype(np.float32)
+        for kw, jitter_of in ((dict(mode=nb.SAMPLING_DET), lambda r: np.full(nc, 0.5, np.float32)),
+                              (dict(mode=nb.SAMPLING_PHILOX, seed=(5 << 32) | 9),
+                               lambda r: O.philox_uniforms((5 << 32) | 9, b + r, 0, nc)),
+                              (dict(mode=nb.SAMPLING_ARRAYS, jitter=jit, u=u), lambda r: jit[r])):
+            _, st = renderer.render_image(cam, W, H, nc, 4, precision="fp16", ray_begin=b, ray_end=e, stages=True, **kw)
+            want = np.stack([O.stratified(cam.near, cam.far, nc, jitter_of(r)) for r in range(n)])
+            assert (st["t_c"] == want).all(), (nc, kw["mode"])
+            assert np.abs(st["dirs"] - O.ray_dirs(O.camera_from_json(CAM), W, H, ray_begin=b, ray_end=e)).max() <= 1.2e-7
