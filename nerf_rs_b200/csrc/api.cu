@@ -96,6 +96,13 @@ struct nerf_ctx {
   DevBuf ray_list, ray_count, dirs_alive;
   uint32_t* h_ray_count = nullptr;
   int64_t rays_total = 0, rays_skipped = 0;  // since timing_start
+  // Two-phase fine pass (NERF_B200_TWO_PHASE=0/1): density for every fine sample first, the colour
+  // branch afterwards over the samples that have density, in groups of fine_sub_rays rays (NERF_B200_FINE_SUB_RAYS) so
+  // that the rows handed from one kernel to the other (512 B per sample with density) fit a fixed buffer even if every
+  // sample has density.  Needs skip_empty (samples without density get rgb = 0) and a 16-bit tensor-core mode.
+  bool two_phase_fine = false;
+  int64_t fine_sub_rays = 81920;
+  DevBuf h8, h8_list, h8_count;
   float select_tau = 12.0f;     // NERF_B200_SELECT_TAU: optical depth behind which no coarse weight survives (T < 6e-6)
   // 8-bit output path: two device frames + two pinned host frames so that the copy of one view overlaps the next render
   DevBuf q8[2], depth, acc;
@@ -214,6 +221,8 @@ int create_common(const TensorMap& coarse, const TensorMap& fine, int device, ne
   if (const char* e = std::getenv("NERF_B200_COARSE_SELECT")) ctx->coarse_select = std::atoi(e) != 0;
   if (const char* e = std::getenv("NERF_B200_SKIP_EMPTY")) ctx->skip_empty = std::atoi(e) != 0;
   if (const char* e = std::getenv("NERF_B200_SKIP_EMPTY_RAYS")) ctx->skip_empty_rays = std::atoi(e) != 0;
+  if (const char* e = std::getenv("NERF_B200_TWO_PHASE")) ctx->two_phase_fine = std::atoi(e) != 0;
+  if (const char* e = std::getenv("NERF_B200_FINE_SUB_RAYS")) ctx->fine_sub_rays = std::max<int64_t>(1, std::atoll(e));
   if (const char* e = std::getenv("NERF_B200_COARSE_STAGES")) ctx->coarse_stages = std::max(1, std::atoi(e));
   if (const char* e = std::getenv("NERF_B200_SELECT_MARGIN")) ctx->select_margin = (float)std::atof(e);
   if (const char* e = std::getenv("NERF_B200_SELECT_TAU")) ctx->select_tau = (float)std::atof(e);
@@ -476,8 +485,38 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
     src.B = nr * nm;
     src.t = c->tf.as<float>();
     dst = SampleDst{c->sigf.as<float>(), c->rgbf.as<float>(), 0.0f, c->skip_empty ? 1 : 0};
+    const bool two_phase = c->two_phase_fine && c->skip_empty &&
+                           (precision == NERF_PREC_MIXED || precision == NERF_PREC_FP16 || precision == NERF_PREC_BF16);
     span_begin(c, ST_MLP_FINE, s);
-    rc = run_mlp(c, NERF_NET_FINE, src, dst, precision, s);
+    if (two_phase) {
+      const TcWeights& wt = c->nets[NERF_NET_FINE].tc[precision == NERF_PREC_BF16 ? 0 : 1];
+      const int64_t sub_max = std::min<int64_t>(nr, c->fine_sub_rays);
+      if ((rc = c->h8.reserve(sub_max * nm * 512)) || (rc = c->h8_list.reserve(sub_max * nm * 4)) ||
+          (rc = c->h8_count.reserve(256)))
+        return rc;
+      for (int64_t r0 = 0; r0 < nr && rc == NERF_OK; r0 += c->fine_sub_rays) {
+        const int64_t ns = std::min<int64_t>(c->fine_sub_rays, nr - r0);
+        SampleSrc s2 = src;
+        s2.dirs = src.dirs + r0 * 3;
+        s2.t = src.t + r0 * nm;
+        s2.B = ns * nm;
+        SampleDst d2 = dst;
+        d2.sigma = dst.sigma + r0 * nm;
+        d2.rgb = dst.rgb + r0 * nm * 3;
+        d2.skip_empty_rgb = 0;
+        d2.h8 = c->h8.as<uint16_t>();
+        d2.h8_list = c->h8_list.as<int32_t>();
+        d2.h8_count = c->h8_count.as<uint32_t>();
+        NERF_CUDA(cudaMemsetAsync(d2.h8_count, 0, 4, s));
+        rc = run_mlp(c, NERF_NET_FINE, s2, d2, precision, s);
+        if (rc == NERF_OK) {
+          NERF_CUDA(launch_mlp_colour(wt, d2.h8, d2.h8_list, d2.h8_count, s2.dirs, nm, d2.rgb, c->sm_count, s));
+          ++c->launches;
+        }
+      }
+    } else {
+      rc = run_mlp(c, NERF_NET_FINE, src, dst, precision, s);
+    }
     span_end(c, s);
     if (rc) return rc;
 
@@ -702,7 +741,7 @@ void nerf_destroy(nerf_ctx* c) {
     }
     for (DevBuf* b : {&c->dirs, &c->tc, &c->sigc, &c->wc, &c->tf, &c->sigf, &c->rgbf, &c->out, &c->in_a, &c->in_b,
                       &c->jit, &c->uni, &c->q8[0], &c->q8[1], &c->depth, &c->acc, &c->sel_list, &c->sel_count, &c->alive[0], &c->alive[1],
-                      &c->ray_list, &c->ray_count, &c->dirs_alive})
+                      &c->ray_list, &c->ray_count, &c->dirs_alive, &c->h8, &c->h8_list, &c->h8_count})
       b->release();
     if (c->h_ray_count) cudaFreeHost(c->h_ray_count);
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);

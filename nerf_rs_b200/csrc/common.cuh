@@ -64,6 +64,13 @@ struct SampleDst {
   // 1: samples whose density is 0 get rgb = 0 instead of the network's colour (their compositing weight is exactly 0,
   // lib.rs:176-195); lets the fused kernel skip the colour branch where a whole tile is empty.  Render launches only.
   int skip_empty_rgb;
+  // Two-phase fine pass (mlp_tc.cu): the launch stops after the density head; a sample with density gets
+  // its dense7 activations (256 16-bit values, the colour branch's input) appended to `h8` and its id to `h8_list`, their
+  // number accumulates in *h8_count (zeroed by the caller); a sample without density gets rgb = 0.  The colour branch
+  // then runs over the list (launch_mlp_colour).  Null: one fused launch.
+  uint16_t* h8;
+  int32_t* h8_list;
+  uint32_t* h8_count;
 };
 
 // Camera constants hoisted out of get_ray_dir (lib.rs:216-226): they do not depend on the pixel, so

@@ -205,7 +205,12 @@ __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t threads) {
 // row of either CTA has density; the weight chunks still stream and are released unread, and the epilogue drains the
 // stale accumulator (finite values: the colour stored for such samples is arbitrary but finite, and never used).
 // forward_batch never skips: the reference returns the colour of every sample.
-template <bool kFp16, bool kRawSigma, bool kSkipEmpty>
+// kStoreH8 (first phase of the two-phase fine pass): the launch ends at the density head like a density-only launch,
+// but dense7's activations are stored to the slot's A tile as usual and, once a row's density is known, quarter 0 of
+// the row block copies the rows WITH density to global memory (512 B each, compacted through one atomicAdd per 32 rows)
+// and stores rgb = 0 for the rows without - the colour branch then runs over the compacted rows only
+// (mlp_colour_kernel below), instead of over every slot that holds at least one such row.
+template <bool kFp16, bool kRawSigma, bool kSkipEmpty, bool kStoreH8 = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ chunks, const SampleSrc src,
               const SampleDst dst, unsigned long long* __restrict__ trace) {
@@ -223,7 +228,7 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();       // 0 = leader (issues the pair's MMAs), 1 = peer
   const int64_t pair_id = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
-  const bool want_rgb = dst.rgb != nullptr;
+  const bool want_rgb = !kStoreH8 && dst.rgb != nullptr;
   const int n_layers = want_rgb ? kNumLayers : 8;
   // kRawSigma launches (coarse first pass) cover a slice of every ray's samples, optionally of listed rays only, whose
   // number the previous stage left on the device
@@ -531,8 +536,9 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
                                             kblock_row0 + s * kActBytes, swz);
           act_ready(s);
         } else {
-          epi_cols<kFp16, true, true, false>(tr, taddr0 + 256u * s, C.bias[7] + colq * 64, C.w_alpha + colq * 64, sig[s],
-                                             kblock_row0 + s * kActBytes, swz);
+          // kStoreH8: h8 goes to the (free) A tile so that rows with density can be copied out below
+          epi_cols<kFp16, true, true, kStoreH8>(tr, taddr0 + 256u * s, C.bias[7] + colq * 64, C.w_alpha + colq * 64,
+                                                sig[s], kblock_row0 + s * kActBytes, swz);
           tc_fence_before();
         }
         float* scratch = reinterpret_cast<float*>(smem + kOffAux + s * kAuxBytes + scratch_off);
@@ -548,6 +554,30 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
 #pragma unroll
           for (uint32_t k = 1; k < 4; ++k) v += reinterpret_cast<const float*>(aux + sw128_offset(row, 32u + 8u * k))[3];
           if (colq == 0 && valid[s]) dst.sigma[g[s]] = kRawSigma ? v : fmaxf(v, 0.0f);
+          if constexpr (kStoreH8) {  // colq == 0 here (kSkipEmpty is off in this instantiation)
+            const bool has = valid[s] && v > 0.0f;
+            const uint32_t m = __ballot_sync(0xffffffffu, has);
+            if (valid[s] && !has) {  // weight exactly 0 in integrate_ray: the colour is never looked at; keep it finite
+              dst.rgb[g[s] * 3 + 0] = 0.0f;
+              dst.rgb[g[s] * 3 + 1] = 0.0f;
+              dst.rgb[g[s] * 3 + 2] = 0.0f;
+            }
+            if (m != 0u) {
+              uint32_t pos0 = 0;
+              if (lane == 0) pos0 = atomicAdd(dst.h8_count, (uint32_t)__popc(m));
+              pos0 = __shfl_sync(0xffffffffu, pos0, 0);
+              if (has) dst.h8_list[pos0 + __popc(m & ((1u << lane) - 1u))] = (int32_t)g[s];
+              // row r of the block: 4 K-blocks x 8 chunks of 16 bytes = one chunk per lane, un-swizzled on the way out
+              const uint8_t* act = smem + kOffAct + s * kActBytes + (uint32_t)(lane >> 3) * kKBlockBytes;
+              uint4* out = reinterpret_cast<uint4*>(dst.h8) + (size_t)pos0 * 32u + lane;
+              for (uint32_t mm = m; mm != 0u; mm &= mm - 1u) {
+                const uint32_t rr = quad * 32u + (uint32_t)(__ffs(mm) - 1);
+                *out = *reinterpret_cast<const uint4*>(act + (rr >> 3) * 1024u + (rr & 7u) * 128u +
+                                                       ((((uint32_t)lane & 7u) ^ (rr & 7u)) << 4));
+                out += 32;
+              }
+            }
+          }
           if constexpr (kSkipEmpty) {
             // does any of this warp's 32 rows need slot s's colour?  Every quarter of a row block reaches the same
             // verdict; quarter 0 sends it to the leader, one word per (CTA, row quadrant)
@@ -641,6 +671,233 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
   __syncthreads();
   cluster_sync_all();  // the peer's shared memory and TMEM stay alive until the pair's last MMA has been consumed
   if (warp == kWarpAlloc) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+  }
+}
+
+
+// ------------------------------------------------------------------------------------------ colour branch alone
+// Second phase of the two-phase fine pass: bottleneck (256 -> 256, no activation, network.rs:218), viewdirs
+// (concat_rows(bottleneck, PE4(dir)) -> 128, ReLU, :220-222) and the f32 rgb head + sigmoid (:223) over the compacted
+// rows the first phase stored (h8 = relu(dense7), 256 16-bit values per sample).  Same operands, same MMA sequence per
+// layer and the same f32 reductions as the fused kernel above, so a sample's colour is bit-identical to the fused
+// kernel's; rows of an MMA tile are independent, so it does not matter which samples share a tile.
+//   A CTA pair works on 256 rows at a time (cta_group::2, M = 256).  Both layers' weight halves are resident in shared
+// memory (64 + 40 KiB per CTA, loaded once with bulk copies from the fused kernel's chunk stream), there is one A tile
+// and one accumulator set (bottleneck: TMEM columns 0..255, viewdirs: 256..383), and the steps of a unit run one after
+// the other - the kernel handles 16 % of the samples for 17 % of the network; what matters is that it exists.  The next
+// unit's rows are fetched into registers while the current one is in the tensor core.
+constexpr int kColThreads = 17 * 32;  // 16 worker warps (load + epilogue, mapped like the fused epilogue) + 1 control warp
+constexpr uint32_t kCOffAct = 0, kCOffAux = kCOffAct + kActBytes, kCOffW8 = kCOffAux + kAuxBytes;
+constexpr uint32_t kCW8Bytes = 4 * 16384, kCW9Bytes = 5 * 8192;
+constexpr uint32_t kCOffW9 = kCOffW8 + kCW8Bytes, kCOffBar = kCOffW9 + kCW9Bytes;
+constexpr uint32_t kCBarW = 0, kCBarIn = 8, kCBarAcc = 16, kCTmemSlot = 24;
+constexpr uint32_t kCSmemBytes = kCOffBar + 64;  // 184.06 KiB
+// byte offsets of the bottleneck and viewdirs chunks in the chunk stream (build_tc_image): 30 K-block images of 32 KiB
+constexpr size_t kChunkOff8 = 30 * 32768, kChunkOff9 = kChunkOff8 + 4 * 32768;
+
+template <bool kFp16>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kColThreads, 1)
+mlp_colour_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ chunks,
+                  const uint16_t* __restrict__ h8, const int32_t* __restrict__ list,
+                  const uint32_t* __restrict__ count, const float* __restrict__ dirs, int S, float* __restrict__ rgb) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  const uint32_t base = smem_u32(smem_raw);
+  if ((base & 1023u) != 0u) __trap();
+  const uint32_t bar_w = base + kCOffBar + kCBarW, bar_in = base + kCOffBar + kCBarIn, bar_acc = base + kCOffBar + kCBarAcc;
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kCOffBar + kCTmemSlot);
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int64_t pair_id = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+  const int64_t n = (int64_t)__ldg(count);
+  const int64_t n_units = (n + 2 * kTileM - 1) / (2 * kTileM);  // unit u: rows [256 u, 256 u + 256), CTA r the r-th half
+
+  if (threadIdx.x == 0) {
+    mbar_init(bar_w, 1);
+    mbar_init(bar_in, 32);  // leader only: one elected arrive per worker warp, both CTAs
+    mbar_init(bar_acc, 1);
+    fence_barrier_init();
+  }
+  if (warp == 16) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(base + kCOffBar + kCTmemSlot),
+                 "r"(512u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // this CTA's halves of the two layers' weights, resident for the whole launch
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(bar_w, kCW8Bytes + kCW9Bytes);
+    for (uint32_t c = 0; c < 4; ++c)  // bottleneck: four [256 x 64] K-block images, rows 128 r .. 128 r + 127 each
+      tma_bulk_g2s(base + kCOffW8 + c * 16384u, chunks + kChunkOff8 + c * 32768u + rank * 16384u, 16384u, bar_w);
+    for (uint32_t c = 0; c < 5; ++c)  // viewdirs: four [128 x 64] K-block images + the PE4(dir) one, rows 64 r .. + 63
+      tma_bulk_g2s(base + kCOffW9 + c * 8192u, chunks + kChunkOff9 + c * 16384u + rank * 8192u, 8192u, bar_w);
+  }
+  mbar_wait(bar_w, 0u);
+  cluster_sync_all();  // the peer's halves have landed too before the leader issues an MMA that reads them
+
+  if (warp == 16) {
+    // ===================================================== MMA issuer (leader CTA)
+    if (rank == 0) {
+      const uint64_t act_desc0 = make_desc(base + kCOffAct), aux_desc0 = make_desc(base + kCOffAux);
+      const uint64_t w8_desc0 = make_desc(base + kCOffW8), w9_desc0 = make_desc(base + kCOffW9);
+      const uint32_t idesc8 = make_idesc(kFp16 ? 1 : 0, 256), idesc9 = make_idesc(kFp16 ? 1 : 0, 128);
+      uint32_t in_par = 0;
+      for (int64_t u = pair_id; u < n_units; u += n_pairs) {
+        mbar_wait(bar_in, in_par);  // h8 rows and PE4(dir) of both CTAs are in shared memory
+        in_par ^= 1u;
+        tc_fence_after();
+        if (elect_one()) {
+#pragma unroll 1
+          for (uint32_t c = 0; c < 4; ++c) {
+            const uint64_t ad = act_desc0 + c * (kKBlockBytes >> 4), bd = w8_desc0 + c * (16384u >> 4);
+            tc_mma2_f16(tmem_base, ad, bd, idesc8, c != 0 ? 1u : 0u);
+            tc_mma2_f16(tmem_base, ad + 2, bd + 2, idesc8, 1u);
+            tc_mma2_f16(tmem_base, ad + 4, bd + 4, idesc8, 1u);
+            tc_mma2_f16(tmem_base, ad + 6, bd + 6, idesc8, 1u);
+          }
+          tc_commit2(bar_acc);
+        }
+        __syncwarp();
+        mbar_wait(bar_in, in_par);  // the bottleneck's output is the A tile now
+        in_par ^= 1u;
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t d1 = tmem_base + 256u;
+#pragma unroll 1
+          for (uint32_t c = 0; c < 4; ++c) {  // the bottleneck's four K-blocks first, PE4(dir) last (network.rs:220)
+            const uint64_t ad = act_desc0 + c * (kKBlockBytes >> 4), bd = w9_desc0 + c * (8192u >> 4);
+            tc_mma2_f16(d1, ad, bd, idesc9, c != 0 ? 1u : 0u);
+            tc_mma2_f16(d1, ad + 2, bd + 2, idesc9, 1u);
+            tc_mma2_f16(d1, ad + 4, bd + 4, idesc9, 1u);
+            tc_mma2_f16(d1, ad + 6, bd + 6, idesc9, 1u);
+          }
+          const uint64_t bd = w9_desc0 + 4u * (8192u >> 4);
+          tc_mma2_f16(d1, aux_desc0, bd, idesc9, 1u);  // K = 32: aux columns 32..63 hold f32 scratch
+          tc_mma2_f16(d1, aux_desc0 + 2, bd + 2, idesc9, 1u);
+          tc_commit2(bar_acc);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ===================================================== workers: one thread per (row, column quarter)
+    const int colq = warp >> 2;
+    const uint32_t quad = (uint32_t)(warp & 3);
+    const uint32_t row = quad * 32u + (uint32_t)lane;
+    const uint32_t r8 = row & 7u;
+    uint8_t* const kblock_row = smem + kCOffAct + (uint32_t)colq * kKBlockBytes + (row >> 3) * 1024u + r8 * 128u;
+    uint8_t* const aux_row = smem + kCOffAux + (row >> 3) * 1024u + r8 * 128u;
+    uint32_t swz[8];
+#pragma unroll
+    for (uint32_t c = 0; c < 8; ++c) swz[c] = (c ^ r8) << 4;
+    const uint32_t scratch_off = sw128_offset(row, 32u + 8u * (uint32_t)colq);
+    const uint32_t row_bar = 1u + quad;
+    const uint32_t taddr = tmem_base + ((quad * 32u) << 16);
+    uint32_t acc_par = 0;
+    Tracer tr{nullptr, 0};
+
+    uint4 q[8];
+    auto fetch = [&](int64_t u) {  // this thread's 128 bytes of row (2 u + rank) * 128 + row: K-block colq
+      const int64_t i = (2 * u + (int64_t)rank) * kTileM + row;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) q[c] = make_uint4(0u, 0u, 0u, 0u);
+      if (i < n) {
+        const uint4* p = reinterpret_cast<const uint4*>(h8 + i * 256 + colq * 64);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) q[c] = __ldg(p + c);
+      }
+    };
+    if (pair_id < n_units) fetch(pair_id);
+    for (int64_t u = pair_id; u < n_units; u += n_pairs) {
+      const int64_t i = (2 * u + (int64_t)rank) * kTileM + row;
+      const bool valid = i < n;
+      int64_t g = 0;
+      float dir[3] = {0.f, 0.f, 0.f};
+      if (valid && colq < 2) {  // quarter 0 stores the colour at g, quarters 0 and 1 write PE4(dir)
+        g = (int64_t)__ldg(list + i);
+        const int64_t ray = g / S;
+        dir[0] = dirs[ray * 3 + 0];
+        dir[1] = dirs[ray * 3 + 1];
+        dir[2] = dirs[ray * 3 + 2];
+      }
+#pragma unroll
+      for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(kblock_row + swz[c]) = q[c];
+      if (colq == 0) write_pe16<kFp16, 0, kDirOctaves>(aux_row, r8, dir);
+      else if (colq == 1) write_pe16<kFp16, 16, kDirOctaves>(aux_row, r8, dir);
+      fence_proxy_async();
+      __syncwarp();
+      if (elect_one()) mbar_arrive_cluster(bar_in, 0u);
+
+      // bottleneck, ActivationType::None: drained into the A tile it was computed from
+      mbar_wait(bar_acc, acc_par);
+      acc_par ^= 1u;
+      tc_fence_after();
+      float unused = 0.0f;
+      epi_cols<kFp16, false, false, true>(tr, taddr + (uint32_t)colq * 64u, C.bias[8] + colq * 64, C.w_alpha, unused,
+                                          kblock_row, swz);
+      fence_proxy_async();
+      tc_fence_before();
+      __syncwarp();
+      if (elect_one()) mbar_arrive_cluster(bar_in, 0u);
+      // the next unit's rows: in flight during the viewdirs layer and the head (issued here, not earlier, so that the
+      // 32 registers do not overlap the 64 of the bottleneck drain)
+      if (u + n_pairs < n_units) fetch(u + n_pairs);
+
+      // viewdirs (ReLU) and the f32 rgb head: 32 columns per warp, as in the fused kernel
+      mbar_wait(bar_acc, acc_par);
+      acc_par ^= 1u;
+      tc_fence_after();
+      uint32_t v[32];
+      tc_ld32(taddr + 256u + 32u * (uint32_t)colq, v);
+      tc_wait_ld();
+      float r0 = 0.f, r1 = 0.f, r2 = 0.f;
+      if (colq == 0) { r0 = C.b_rgb[0]; r1 = C.b_rgb[1]; r2 = C.b_rgb[2]; }
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int k = colq * 32 + j;
+        const float c = fmaxf(__uint_as_float(v[j]) + C.bias[9][k], 0.0f);
+        r0 = fmaf(c, C.w_rgb[k * 3 + 0], r0);
+        r1 = fmaf(c, C.w_rgb[k * 3 + 1], r1);
+        r2 = fmaf(c, C.w_rgb[k * 3 + 2], r2);
+      }
+      tc_fence_before();
+      if (colq != 0) {
+        float* scratch = reinterpret_cast<float*>(smem + kCOffAux + scratch_off);
+        scratch[0] = r0;
+        scratch[1] = r1;
+        scratch[2] = r2;
+      }
+      named_bar_sync(row_bar, 128);
+      if (colq == 0) {
+        const uint8_t* aux = smem + kCOffAux;
+#pragma unroll
+        for (uint32_t k = 1; k < 4; ++k) {
+          const float* sc = reinterpret_cast<const float*>(aux + sw128_offset(row, 32u + 8u * k));
+          r0 += sc[0];
+          r1 += sc[1];
+          r2 += sc[2];
+        }
+        if (valid) {
+          rgb[g * 3 + 0] = 1.0f / (1.0f + expf(-r0));  // network.rs:165
+          rgb[g * 3 + 1] = 1.0f / (1.0f + expf(-r1));
+          rgb[g * 3 + 2] = 1.0f / (1.0f + expf(-r2));
+        }
+      }
+      named_bar_sync(row_bar, 128);  // the scratch chunks are rewritten by the next unit
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 16) {
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
   }
 }
@@ -756,11 +1013,17 @@ void free_tc_weights(TcWeights* w) {
 }
 
 cudaError_t init_mlp_tc() {  // once per process and device, at context creation
-  const void* kernels[5] = {(const void*)mlp_tc_kernel<true, true, false>, (const void*)mlp_tc_kernel<true, false, true>,
+  const void* kernels[7] = {(const void*)mlp_tc_kernel<true, true, false>, (const void*)mlp_tc_kernel<true, false, true>,
                             (const void*)mlp_tc_kernel<true, false, false>, (const void*)mlp_tc_kernel<false, false, true>,
-                            (const void*)mlp_tc_kernel<false, false, false>};
+                            (const void*)mlp_tc_kernel<false, false, false>,
+                            (const void*)mlp_tc_kernel<true, false, false, true>,
+                            (const void*)mlp_tc_kernel<false, false, false, true>};
   for (const void* k : kernels) {
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e != cudaSuccess) return e;
+  }
+  for (const void* k : {(const void*)mlp_colour_kernel<true>, (const void*)mlp_colour_kernel<false>}) {
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCSmemBytes);
     if (e != cudaSuccess) return e;
   }
   return cudaSuccess;
@@ -794,8 +1057,13 @@ cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src_in, const Sam
   const bool raw = dst.sigma_floor < 0.0f;
   if (raw && (w.fmt != 1 || dst.rgb != nullptr)) return cudaErrorInvalidValue;  // only the fp16 density-only pass has it
   const bool skip = dst.skip_empty_rgb != 0 && dst.rgb != nullptr;
-  const int which = raw ? 0 : (w.fmt == 1 ? (skip ? 1 : 2) : (skip ? 3 : 4));
+  const bool h8 = dst.h8 != nullptr;  // first phase of the two-phase fine pass
+  if (h8 && (raw || dst.rgb == nullptr || dst.h8_list == nullptr || dst.h8_count == nullptr || src.B > 0x7fffffff))
+    return cudaErrorInvalidValue;
+  const int which = raw ? 0 : (h8 ? (w.fmt == 1 ? 5 : 6) : (w.fmt == 1 ? (skip ? 1 : 2) : (skip ? 3 : 4)));
   switch (which) {
+    case 5: mlp_tc_kernel<true, false, false, true><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace); break;
+    case 6: mlp_tc_kernel<false, false, false, true><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace); break;
     case 0: mlp_tc_kernel<true, true, false><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace); break;
     case 1: mlp_tc_kernel<true, false, true><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace); break;
     case 2: mlp_tc_kernel<true, false, false><<<grid, kThreads, kSmemBytes, s>>>(w.consts, w.d_chunks, src, dst, trace); break;
@@ -814,6 +1082,17 @@ cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src_in, const Sam
     }
   }
   return e;
+}
+
+cudaError_t launch_mlp_colour(const TcWeights& w, const uint16_t* d_h8, const int32_t* d_list, const uint32_t* d_count,
+                              const float* d_dirs, int S, float* d_rgb, int sm_count, cudaStream_t s) {
+  if (w.fmt != 0 && w.fmt != 1) return cudaErrorInvalidValue;
+  const int grid = 2 * (sm_count / 2);  // the number of rows is on the device: a full persistent grid
+  if (w.fmt == 1)
+    mlp_colour_kernel<true><<<grid, kColThreads, kCSmemBytes, s>>>(w.consts, w.d_chunks, d_h8, d_list, d_count, d_dirs, S, d_rgb);
+  else
+    mlp_colour_kernel<false><<<grid, kColThreads, kCSmemBytes, s>>>(w.consts, w.d_chunks, d_h8, d_list, d_count, d_dirs, S, d_rgb);
+  return cudaGetLastError();
 }
 
 }  // namespace nerf
