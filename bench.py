@@ -49,8 +49,11 @@ PRECISION_NOTE = {
 }
 # dram__bytes_read.sum + dram__bytes_write.sum of the fine-pass launch, 800x800 c64+f128: a CONSTANT copied from one
 # `ncu --set full` capture (file below), not measured by this run
-NCU_FINE_DRAM_GB = 0.518 + 1.915  # mlp_tc_kernel<1,0,1>, the fine pass of the reference frame
-NCU_FINE_DRAM_SOURCE = "profiles/r02_frame_ncu_full_summary.csv"
+# the fine pass of the reference frame: 16 x mlp_tc_kernel<1,0,0,1> (0.55 GB read, 10.95 GB written: densities, zero colours
+# and the 512-byte rows of the 16 % of the samples that have density) + 16 x mlp_colour_kernel (10.17 GB read, 0.27 GB
+# written).  The fused single launch it replaced: 0.518 + 1.915 GB (profiles/r02_frame_ncu_full_summary.csv)
+NCU_FINE_DRAM_GB = 0.549 + 10.949 + 10.166 + 0.269
+NCU_FINE_DRAM_SOURCE = "profiles/r02_two_phase_ncu_full_summary.csv"
 
 
 def load_peaks():
@@ -395,7 +398,11 @@ def gpu_arm(args):
         ach = fine_flop / (mf * 1e-3) / 1e12
         frame_tflops = n_rays * (NC * FLOP_COARSE + (NC + NF) * FLOP_FINE) / (ms * 1e-3) / 1e12
         fine_kernel = {"fp16x3": "mlp_tc_x3_kernel (fine pass; 3 MMAs per product, credited once)",
-                       "fp32": "mlp_fp32_kernel (fine pass; CUDA cores)"}.get(args.precision, "mlp_tc_kernel (fine pass)")
+                       "fp32": "mlp_fp32_kernel (fine pass; CUDA cores)",
+                       "tf32": "mlp_tc_tf32_kernel (fine pass)"}.get(
+            args.precision, "fine pass = per group of 40 960 rays one mlp_tc_kernel<store h8> launch (trunk + density head, "
+                            "every sample) and one mlp_colour_kernel launch (colour branch, the samples with density); "
+                            "credited the reference's FLOP for every sample, stage time = all launches of the pass")
         coarse_kernel = {"fp16x3": "mlp_tc_x3_kernel (coarse pass, sigma only; 3 MMAs per product, credited once)",
                          "fp32": "mlp_fp32_kernel (coarse pass)",
                          "mixed": "mlp_tc_kernel fp16 over every coarse sample + coarse_select_kernel + mlp_tc_x3_kernel over "
@@ -451,7 +458,7 @@ def gpu_arm(args):
                                      if dominant_is_fine and args.precision in ("fp16", "bf16", "mixed") else None),
                          "traffic_unit": "GB per launch",
                          "traffic_source": f"constant from one ncu --set full capture ({NCU_FINE_DRAM_SOURCE}, dram read + "
-                                           "write of the fine-pass launch), scaled to this rank's share of the rays; not "
+                                           "write summed over the fine pass's launches), scaled to this rank's share of the rays; not "
                                            "measured by this run"},
             "roofline_other": {"bound": "tensor", "kernel": coarse_kernel if dominant_is_fine else fine_kernel,
                                "achieved": c_ach if dominant_is_fine else ach, "peak": sustained, "unit": "TFLOP/s",

@@ -100,8 +100,8 @@ struct nerf_ctx {
   // branch afterwards over the samples that have density, in groups of fine_sub_rays rays (NERF_B200_FINE_SUB_RAYS) so
   // that the rows handed from one kernel to the other (512 B per sample with density) fit a fixed buffer even if every
   // sample has density.  Needs skip_empty (samples without density get rgb = 0) and a 16-bit tensor-core mode.
-  bool two_phase_fine = false;
-  int64_t fine_sub_rays = 81920;
+  bool two_phase_fine = true;
+  int64_t fine_sub_rays = 40960;
   DevBuf h8, h8_list, h8_count;
   float select_tau = 12.0f;     // NERF_B200_SELECT_TAU: optical depth behind which no coarse weight survives (T < 6e-6)
   // 8-bit output path: two device frames + two pinned host frames so that the copy of one view overlaps the next render

@@ -685,8 +685,10 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
 //   A CTA pair works on 256 rows at a time (cta_group::2, M = 256).  Both layers' weight halves are resident in shared
 // memory (64 + 40 KiB per CTA, loaded once with bulk copies from the fused kernel's chunk stream), there is one A tile
 // and one accumulator set (bottleneck: TMEM columns 0..255, viewdirs: 256..383), and the steps of a unit run one after
-// the other - the kernel handles 16 % of the samples for 17 % of the network; what matters is that it exists.  The next
-// unit's rows are fetched into registers while the current one is in the tensor core.
+// the other - the kernel handles 16 % of the samples for 17 % of the network (6 ms of the 800x800 frame).  The next
+// unit's rows are fetched into registers while the current one is in the tensor core.  (Running these two layers
+// through the fused kernel's own ring and two-slot schedule instead - A tiles loaded from the stored rows - was built
+// and measured: bit-identical and 1.3 ms slower per frame, because a quad's loads are exposed twice; not kept.)
 constexpr int kColThreads = 17 * 32;  // 16 worker warps (load + epilogue, mapped like the fused epilogue) + 1 control warp
 constexpr uint32_t kCOffAct = 0, kCOffAux = kCOffAct + kActBytes, kCOffW8 = kCOffAux + kAuxBytes;
 constexpr uint32_t kCW8Bytes = 4 * 16384, kCW9Bytes = 5 * 8192;

@@ -85,7 +85,7 @@ def test_philox_default_sampling_at_reference_counts(renderer, cam, onets, ocam,
 
 def _fresh(env):
     keys = ("NERF_B200_COARSE_SELECT", "NERF_B200_CHUNK_RAYS", "NERF_B200_SELECT_MARGIN", "NERF_B200_SELECT_TAU",
-            "NERF_B200_SKIP_EMPTY", "NERF_B200_COARSE_STAGES")
+            "NERF_B200_SKIP_EMPTY", "NERF_B200_COARSE_STAGES", "NERF_B200_TWO_PHASE", "NERF_B200_FINE_SUB_RAYS")
     saved = {k: os.environ.pop(k, None) for k in keys}
     os.environ.update(env)
     try:
@@ -347,3 +347,40 @@ def test_stratified_samples_bit_exact_for_every_count_and_mode(renderer, cam):
             want = np.stack([O.stratified(cam.near, cam.far, nc, jitter_of(r)) for r in range(n)])
             assert (st["t_c"] == want).all(), (nc, kw["mode"])
             assert np.abs(st["dirs"] - O.ray_dirs(O.camera_from_json(CAM), W, H, ray_begin=b, ray_end=e)).max() <= 1.2e-7
+
+
+@pytest.mark.parametrize("prec", ["mixed", "fp16", "bf16"])
+def test_two_phase_fine_pass_is_invisible(renderer, cam, prec):
+    """The fine pass runs as two launches per group of rays (density for every sample; the colour branch over the
+    samples that have density): frames, depth and opacity bit-identical to the fused launch
+    (NERF_B200_TWO_PHASE=0), with groups of 700 rays (ragged last group, groups without any density) as with one group,
+    and together with the opt-in skipping of rays."""
+    fused = _fresh({"NERF_B200_TWO_PHASE": "0"})
+    groups = _fresh({"NERF_B200_TWO_PHASE": "1", "NERF_B200_FINE_SUB_RAYS": "700"})
+    try:
+        W, H = 160, 120
+        for kw in (dict(mode=nb.SAMPLING_DET), dict(mode=nb.SAMPLING_PHILOX, seed=12)):
+            a = fused.render_image(cam, W, H, 64, 128, precision=prec, **kw)
+            n_fused = fused.timing()["kernel_launches"]
+            b = renderer.render_image(cam, W, H, 64, 128, precision=prec, **kw)
+            n_two = renderer.timing()["kernel_launches"]
+            assert n_two == n_fused + 1  # one group: the fused launch became two
+            c = groups.render_image(cam, W, H, 64, 128, precision=prec, **kw)
+            assert groups.timing()["kernel_launches"] > n_two  # 28 groups of two launches
+            assert (a == b).all() and (a == c).all() and np.isfinite(b).all()
+        ra, da, aa = fused.render_aux(cam, W, H, 64, 128, precision=prec)
+        for r in (renderer, groups):
+            rb, db, ab = r.render_aux(cam, W, H, 64, 128, precision=prec)
+            assert (ra == rb).all() and (da == db).all() and (aa == ab).all()
+        # other sample counts (192 is the only one with kernels of its own elsewhere in the pipeline)
+        for nc, nf in ((16, 24), (64, 0), (32, 96)):
+            assert (fused.render_image(cam, 64, 48, nc, nf, precision=prec) ==
+                    groups.render_image(cam, 64, 48, nc, nf, precision=prec)).all(), (nc, nf)
+        # with rays skipped (opt-in): the list of rays and the list of samples compose
+        for r in (fused, groups):
+            r.set_option(nb.OPT_SKIP_EMPTY_RAYS, 1)
+        assert (fused.render_image(cam, W, H, 64, 128, precision=prec) ==
+                groups.render_image(cam, W, H, 64, 128, precision=prec)).all()
+    finally:
+        fused.close()
+        groups.close()
