@@ -491,7 +491,8 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
     if (two_phase) {
       const TcWeights& wt = c->nets[NERF_NET_FINE].tc[precision == NERF_PREC_BF16 ? 0 : 1];
       const int64_t sub_max = std::min<int64_t>(nr, c->fine_sub_rays);
-      if ((rc = c->h8.reserve(sub_max * nm * 512)) || (rc = c->h8_list.reserve(sub_max * nm * 4)) ||
+      // rows are stored as whole [128 x 256] tile images; a CTA pair of the colour kernel reads two tiles at a time
+      if ((rc = c->h8.reserve(((sub_max * nm + 255) / 256) * 256 * 512)) || (rc = c->h8_list.reserve(sub_max * nm * 16)) ||
           (rc = c->h8_count.reserve(256)))
         return rc;
       for (int64_t r0 = 0; r0 < nr && rc == NERF_OK; r0 += c->fine_sub_rays) {
@@ -505,12 +506,12 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
         d2.rgb = dst.rgb + r0 * nm * 3;
         d2.skip_empty_rgb = 0;
         d2.h8 = c->h8.as<uint16_t>();
-        d2.h8_list = c->h8_list.as<int32_t>();
+        d2.h8_meta = c->h8_list.as<float4>();
         d2.h8_count = c->h8_count.as<uint32_t>();
         NERF_CUDA(cudaMemsetAsync(d2.h8_count, 0, 4, s));
         rc = run_mlp(c, NERF_NET_FINE, s2, d2, precision, s);
         if (rc == NERF_OK) {
-          NERF_CUDA(launch_mlp_colour(wt, d2.h8, d2.h8_list, d2.h8_count, s2.dirs, nm, d2.rgb, c->sm_count, s));
+          NERF_CUDA(launch_mlp_colour(wt, d2.h8, d2.h8_meta, d2.h8_count, d2.rgb, c->sm_count, s));
           ++c->launches;
         }
       }

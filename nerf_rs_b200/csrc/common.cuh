@@ -65,11 +65,11 @@ struct SampleDst {
   // lib.rs:176-195); lets the fused kernel skip the colour branch where a whole tile is empty.  Render launches only.
   int skip_empty_rgb;
   // Two-phase fine pass (mlp_tc.cu): the launch stops after the density head; a sample with density gets
-  // its dense7 activations (256 16-bit values, the colour branch's input) appended to `h8` and its id to `h8_list`, their
-  // number accumulates in *h8_count (zeroed by the caller); a sample without density gets rgb = 0.  The colour branch
-  // then runs over the list (launch_mlp_colour).  Null: one fused launch.
+  // its dense7 activations (256 16-bit values, the colour branch's input) appended to `h8` and {ray direction, sample
+  // id as bits} to `h8_meta`, their number accumulates in *h8_count (zeroed by the caller); a sample without density
+  // gets rgb = 0.  The colour branch then runs over those rows (launch_mlp_colour).  Null: one fused launch.
   uint16_t* h8;
-  int32_t* h8_list;
+  float4* h8_meta;
   uint32_t* h8_count;
 };
 

@@ -566,15 +566,21 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
               uint32_t pos0 = 0;
               if (lane == 0) pos0 = atomicAdd(dst.h8_count, (uint32_t)__popc(m));
               pos0 = __shfl_sync(0xffffffffu, pos0, 0);
-              if (has) dst.h8_list[pos0 + __popc(m & ((1u << lane) - 1u))] = (int32_t)g[s];
-              // row r of the block: 4 K-blocks x 8 chunks of 16 bytes = one chunk per lane, un-swizzled on the way out
+              if (has)  // what the colour branch needs besides h8: the ray's direction and where the colour goes
+                dst.h8_meta[pos0 + __popc(m & ((1u << lane) - 1u))] =
+                    make_float4(dir[s][0], dir[s][1], dir[s][2], __int_as_float((int32_t)g[s]));
+              // A row is 4 K-blocks x 8 chunks of 16 bytes = one chunk per lane.  Stored row p goes to row p % 128 of tile
+              // p / 128 of dst.h8, each tile being the exact SWIZZLE_128B shared-memory image of a [128 x 256] A operand
+              // (64 KiB), so that the colour kernel brings a tile in with bulk copies and no register staging.
               const uint8_t* act = smem + kOffAct + s * kActBytes + (uint32_t)(lane >> 3) * kKBlockBytes;
-              uint4* out = reinterpret_cast<uint4*>(dst.h8) + (size_t)pos0 * 32u + lane;
-              for (uint32_t mm = m; mm != 0u; mm &= mm - 1u) {
+              uint8_t* const out0 = reinterpret_cast<uint8_t*>(dst.h8) + (uint32_t)(lane >> 3) * kKBlockBytes;
+              uint32_t p = pos0;
+              for (uint32_t mm = m; mm != 0u; mm &= mm - 1u, ++p) {
                 const uint32_t rr = quad * 32u + (uint32_t)(__ffs(mm) - 1);
-                *out = *reinterpret_cast<const uint4*>(act + (rr >> 3) * 1024u + (rr & 7u) * 128u +
-                                                       ((((uint32_t)lane & 7u) ^ (rr & 7u)) << 4));
-                out += 32;
+                const uint4 val = *reinterpret_cast<const uint4*>(act + (rr >> 3) * 1024u + (rr & 7u) * 128u +
+                                                                  ((((uint32_t)lane & 7u) ^ (rr & 7u)) << 4));
+                *reinterpret_cast<uint4*>(out0 + (size_t)(p >> 7) * kActBytes + ((p & 127u) >> 3) * 1024u + (p & 7u) * 128u +
+                                          ((((uint32_t)lane & 7u) ^ (p & 7u)) << 4)) = val;
               }
             }
           }
@@ -679,50 +685,64 @@ mlp_tc_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ ch
 // ------------------------------------------------------------------------------------------ colour branch alone
 // Second phase of the two-phase fine pass: bottleneck (256 -> 256, no activation, network.rs:218), viewdirs
 // (concat_rows(bottleneck, PE4(dir)) -> 128, ReLU, :220-222) and the f32 rgb head + sigmoid (:223) over the compacted
-// rows the first phase stored (h8 = relu(dense7), 256 16-bit values per sample).  Same operands, same MMA sequence per
-// layer and the same f32 reductions as the fused kernel above, so a sample's colour is bit-identical to the fused
-// kernel's; rows of an MMA tile are independent, so it does not matter which samples share a tile.
+// rows the first phase stored (h8 = relu(dense7), 256 16-bit values per sample, as [128 x 256] tile images).  Same
+// operands, same MMA sequence per layer and the same f32 reductions as the fused kernel above, so a sample's colour is
+// bit-identical to the fused kernel's; rows of an MMA tile are independent, so it does not matter which samples share
+// a tile.
 //   A CTA pair works on 256 rows at a time (cta_group::2, M = 256).  Both layers' weight halves are resident in shared
-// memory (64 + 40 KiB per CTA, loaded once with bulk copies from the fused kernel's chunk stream), there is one A tile
-// and one accumulator set (bottleneck: TMEM columns 0..255, viewdirs: 256..383), and the steps of a unit run one after
-// the other - the kernel handles 16 % of the samples for 17 % of the network (6 ms of the 800x800 frame).  The next
-// unit's rows are fetched into registers while the current one is in the tensor core.  (Running these two layers
-// through the fused kernel's own ring and two-slot schedule instead - A tiles loaded from the stored rows - was built
-// and measured: bit-identical and 1.3 ms slower per frame, because a quad's loads are exposed twice; not kept.)
-constexpr int kColThreads = 17 * 32;  // 16 worker warps (load + epilogue, mapped like the fused epilogue) + 1 control warp
-constexpr uint32_t kCOffAct = 0, kCOffAux = kCOffAct + kActBytes, kCOffW8 = kCOffAux + kAuxBytes;
+// memory (64 + 40 KiB per CTA, bulk-copied once from the fused kernel's chunk stream).  A unit's rows come in with bulk
+// copies straight into the one A tile.  The bottleneck's output does NOT go back into that tile: it stays in TENSOR
+// MEMORY as the viewdirs layer's A operand (tcgen05.mma with A from TMEM: row = lane, two 16-bit elements per 32-bit
+// column), which frees the A tile as soon as the bottleneck MMAs of unit u have completed - the rows of unit u + 1
+// arrive while unit u's viewdirs layer runs, and the bottleneck MMAs of unit u + 1 run under unit u's rgb head.
+// TMEM: bottleneck accumulator columns 0..255, viewdirs accumulator 256..383, the bottleneck's 256 16-bit outputs
+// packed in columns 384..511.  PE4(dir) tiles alternate between two aux buffers.
+//   How it got here (800x800 frame, ncu; every version bit-identical to the fused kernel): one A tile that the
+// bottleneck was drained back into, every step of a unit after the other, rows through registers - 6.2 ms, tensor
+// pipe 31 %; A from TMEM - 5.1 ms (a timeline showed the nine loads of a unit taking 1 500 - 5 700 cycles to ISSUE:
+// 64 KiB per SM and unit is more than the L1 miss path sustains, coalesced or not); rows by bulk copy - 3.8 ms, tensor
+// pipe 48 %, period 6 000 cycles for 3 750 of MMA.  Under the frame's power cap the last step is worth less than
+// under ncu: what the cap prices is energy, and a kernel that idles costs little of it.
+constexpr int kColThreads = 17 * 32;  // 16 worker warps (mapped like the fused epilogue) + 1 control warp
 constexpr uint32_t kCW8Bytes = 4 * 16384, kCW9Bytes = 5 * 8192;
-constexpr uint32_t kCOffW9 = kCOffW8 + kCW8Bytes, kCOffBar = kCOffW9 + kCW9Bytes;
-constexpr uint32_t kCBarW = 0, kCBarIn = 8, kCBarAcc = 16, kCTmemSlot = 24;
-constexpr uint32_t kCSmemBytes = kCOffBar + 64;  // 184.06 KiB
 // byte offsets of the bottleneck and viewdirs chunks in the chunk stream (build_tc_image): 30 K-block images of 32 KiB
 constexpr size_t kChunkOff8 = 30 * 32768, kChunkOff9 = kChunkOff8 + 4 * 32768;
+constexpr uint32_t kTOffAct = 0, kTOffAux = kTOffAct + kActBytes, kTOffW8 = kTOffAux + 2 * kAuxBytes;
+constexpr uint32_t kTOffW9 = kTOffW8 + kCW8Bytes, kTOffBar = kTOffW9 + kCW9Bytes;
+constexpr uint32_t kTBarW = 0, kTBarIn8 = 8, kTBarIn9 = 16, kTBarAcc8 = 24, kTBarAcc9 = 32, kTTmemSlot = 40, kTBarRows = 48;
+constexpr uint32_t kTSmemBytes = kTOffBar + 64;  // 200.06 KiB
+constexpr uint32_t kTColA9 = 384;
 
 template <bool kFp16>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kColThreads, 1)
 mlp_colour_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict__ chunks,
-                  const uint16_t* __restrict__ h8, const int32_t* __restrict__ list,
-                  const uint32_t* __restrict__ count, const float* __restrict__ dirs, int S, float* __restrict__ rgb) {
+                     const uint16_t* __restrict__ h8, const float4* __restrict__ meta,
+                     const uint32_t* __restrict__ count, float* __restrict__ rgb) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
   const uint32_t base = smem_u32(smem_raw);
   if ((base & 1023u) != 0u) __trap();
-  const uint32_t bar_w = base + kCOffBar + kCBarW, bar_in = base + kCOffBar + kCBarIn, bar_acc = base + kCOffBar + kCBarAcc;
-  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kCOffBar + kCTmemSlot);
+  const uint32_t bar0 = base + kTOffBar;
+  const uint32_t bar_w = bar0 + kTBarW, bar_in8 = bar0 + kTBarIn8, bar_in9 = bar0 + kTBarIn9, bar_acc8 = bar0 + kTBarAcc8,
+                 bar_acc9 = bar0 + kTBarAcc9, bar_rows = bar0 + kTBarRows;
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kTOffBar + kTTmemSlot);
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const int64_t pair_id = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const int64_t n = (int64_t)__ldg(count);
-  const int64_t n_units = (n + 2 * kTileM - 1) / (2 * kTileM);  // unit u: rows [256 u, 256 u + 256), CTA r the r-th half
+  const int64_t n_units = (n + 2 * kTileM - 1) / (2 * kTileM);
 
   if (threadIdx.x == 0) {
     mbar_init(bar_w, 1);
-    mbar_init(bar_in, 32);  // leader only: one elected arrive per worker warp, both CTAs
-    mbar_init(bar_acc, 1);
+    mbar_init(bar_in8, 32);  // leader only: one elected arrive per worker warp, both CTAs
+    mbar_init(bar_in9, 32);
+    mbar_init(bar_acc8, 1);
+    mbar_init(bar_acc9, 1);
+    mbar_init(bar_rows, 1);  // this CTA's tile of rows (bulk copies, expect_tx)
     fence_barrier_init();
   }
   if (warp == 16) {
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(base + kCOffBar + kCTmemSlot),
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(base + kTOffBar + kTTmemSlot),
                  "r"(512u)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
@@ -733,27 +753,25 @@ mlp_colour_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict_
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // this CTA's halves of the two layers' weights, resident for the whole launch
   if (threadIdx.x == 0) {
     mbar_arrive_expect_tx(bar_w, kCW8Bytes + kCW9Bytes);
-    for (uint32_t c = 0; c < 4; ++c)  // bottleneck: four [256 x 64] K-block images, rows 128 r .. 128 r + 127 each
-      tma_bulk_g2s(base + kCOffW8 + c * 16384u, chunks + kChunkOff8 + c * 32768u + rank * 16384u, 16384u, bar_w);
-    for (uint32_t c = 0; c < 5; ++c)  // viewdirs: four [128 x 64] K-block images + the PE4(dir) one, rows 64 r .. + 63
-      tma_bulk_g2s(base + kCOffW9 + c * 8192u, chunks + kChunkOff9 + c * 16384u + rank * 8192u, 8192u, bar_w);
+    for (uint32_t c = 0; c < 4; ++c)
+      tma_bulk_g2s(base + kTOffW8 + c * 16384u, chunks + kChunkOff8 + c * 32768u + rank * 16384u, 16384u, bar_w);
+    for (uint32_t c = 0; c < 5; ++c)
+      tma_bulk_g2s(base + kTOffW9 + c * 8192u, chunks + kChunkOff9 + c * 16384u + rank * 8192u, 8192u, bar_w);
   }
   mbar_wait(bar_w, 0u);
-  cluster_sync_all();  // the peer's halves have landed too before the leader issues an MMA that reads them
+  cluster_sync_all();
 
   if (warp == 16) {
     // ===================================================== MMA issuer (leader CTA)
     if (rank == 0) {
-      const uint64_t act_desc0 = make_desc(base + kCOffAct), aux_desc0 = make_desc(base + kCOffAux);
-      const uint64_t w8_desc0 = make_desc(base + kCOffW8), w9_desc0 = make_desc(base + kCOffW9);
+      const uint64_t act_desc0 = make_desc(base + kTOffAct), aux_desc0 = make_desc(base + kTOffAux);
+      const uint64_t w8_desc0 = make_desc(base + kTOffW8), w9_desc0 = make_desc(base + kTOffW9);
       const uint32_t idesc8 = make_idesc(kFp16 ? 1 : 0, 256), idesc9 = make_idesc(kFp16 ? 1 : 0, 128);
-      uint32_t in_par = 0;
+      uint32_t par = 0, buf = 0;
       for (int64_t u = pair_id; u < n_units; u += n_pairs) {
-        mbar_wait(bar_in, in_par);  // h8 rows and PE4(dir) of both CTAs are in shared memory
-        in_par ^= 1u;
+        mbar_wait(bar_in8, par);  // rows and PE4(dir) of unit u in shared memory; bottleneck accumulator drained
         tc_fence_after();
         if (elect_one()) {
 #pragma unroll 1
@@ -764,28 +782,29 @@ mlp_colour_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict_
             tc_mma2_f16(tmem_base, ad + 4, bd + 4, idesc8, 1u);
             tc_mma2_f16(tmem_base, ad + 6, bd + 6, idesc8, 1u);
           }
-          tc_commit2(bar_acc);
+          tc_commit2(bar_acc8);
         }
         __syncwarp();
-        mbar_wait(bar_in, in_par);  // the bottleneck's output is the A tile now
-        in_par ^= 1u;
+        mbar_wait(bar_in9, par);  // the bottleneck's output of unit u is in tensor memory; viewdirs accumulator read
         tc_fence_after();
         if (elect_one()) {
-          const uint32_t d1 = tmem_base + 256u;
+          const uint32_t d1 = tmem_base + 256u, a9 = tmem_base + kTColA9;
 #pragma unroll 1
           for (uint32_t c = 0; c < 4; ++c) {  // the bottleneck's four K-blocks first, PE4(dir) last (network.rs:220)
-            const uint64_t ad = act_desc0 + c * (kKBlockBytes >> 4), bd = w9_desc0 + c * (8192u >> 4);
-            tc_mma2_f16(d1, ad, bd, idesc9, c != 0 ? 1u : 0u);
-            tc_mma2_f16(d1, ad + 2, bd + 2, idesc9, 1u);
-            tc_mma2_f16(d1, ad + 4, bd + 4, idesc9, 1u);
-            tc_mma2_f16(d1, ad + 6, bd + 6, idesc9, 1u);
+            const uint64_t bd = w9_desc0 + c * (8192u >> 4);
+            tc_mma2_f16_ts(d1, a9 + c * 32u, bd, idesc9, c != 0 ? 1u : 0u);
+            tc_mma2_f16_ts(d1, a9 + c * 32u + 8u, bd + 2, idesc9, 1u);
+            tc_mma2_f16_ts(d1, a9 + c * 32u + 16u, bd + 4, idesc9, 1u);
+            tc_mma2_f16_ts(d1, a9 + c * 32u + 24u, bd + 6, idesc9, 1u);
           }
-          const uint64_t bd = w9_desc0 + 4u * (8192u >> 4);
-          tc_mma2_f16(d1, aux_desc0, bd, idesc9, 1u);  // K = 32: aux columns 32..63 hold f32 scratch
-          tc_mma2_f16(d1, aux_desc0 + 2, bd + 2, idesc9, 1u);
-          tc_commit2(bar_acc);
+          const uint64_t bd = w9_desc0 + 4u * (8192u >> 4), auxd = aux_desc0 + buf * (kAuxBytes >> 4);
+          tc_mma2_f16(d1, auxd, bd, idesc9, 1u);  // K = 32: aux columns 32..63 hold f32 scratch
+          tc_mma2_f16(d1, auxd + 2, bd + 2, idesc9, 1u);
+          tc_commit2(bar_acc9);
         }
         __syncwarp();
+        par ^= 1u;
+        buf ^= 1u;
       }
     }
   } else {
@@ -794,67 +813,93 @@ mlp_colour_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict_
     const uint32_t quad = (uint32_t)(warp & 3);
     const uint32_t row = quad * 32u + (uint32_t)lane;
     const uint32_t r8 = row & 7u;
-    uint8_t* const kblock_row = smem + kCOffAct + (uint32_t)colq * kKBlockBytes + (row >> 3) * 1024u + r8 * 128u;
-    uint8_t* const aux_row = smem + kCOffAux + (row >> 3) * 1024u + r8 * 128u;
-    uint32_t swz[8];
-#pragma unroll
-    for (uint32_t c = 0; c < 8; ++c) swz[c] = (c ^ r8) << 4;
-    const uint32_t scratch_off = sw128_offset(row, 32u + 8u * (uint32_t)colq);
+    const uint32_t aux_row_off = kTOffAux + (row >> 3) * 1024u + r8 * 128u;
+    const uint32_t scratch_off = kTOffAux + sw128_offset(row, 32u + 8u * (uint32_t)colq);
     const uint32_t row_bar = 1u + quad;
     const uint32_t taddr = tmem_base + ((quad * 32u) << 16);
-    uint32_t acc_par = 0;
-    Tracer tr{nullptr, 0};
+    uint32_t par = 0, buf = 0;
 
-    uint4 q[8];
-    auto fetch = [&](int64_t u) {  // this thread's 128 bytes of row (2 u + rank) * 128 + row: K-block colq
-      const int64_t i = (2 * u + (int64_t)rank) * kTileM + row;
+    // The rows of a unit come in with four 16 KiB bulk copies straight into the A tile (the first phase stored them as
+    // the tile's shared-memory image); warp 0 issues them as soon as the tile is free and waits for them before it tells
+    // the issuer.  (Through registers - 16 bytes per lane, ld.global + st.shared - the loads of a unit took 1 500 to
+    // 5 700 cycles to ISSUE: 64 KiB per SM and unit is more than the L1 miss path sustains.)  {ray direction, sample id}
+    // of the row is prefetched into registers.
+    float4 meta_f = make_float4(0.f, 0.f, 0.f, 0.f);
+    bool valid_f = false;
+    uint32_t rows_par = 0;
+    auto copy_rows = [&](int64_t u) {  // warp 0 only
+      if (warp == 0 && elect_one()) {
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(h8) + (size_t)(2 * u + (int64_t)rank) * kActBytes;
+        mbar_arrive_expect_tx(bar_rows, kActBytes);
 #pragma unroll
-      for (int c = 0; c < 8; ++c) q[c] = make_uint4(0u, 0u, 0u, 0u);
-      if (i < n) {
-        const uint4* p = reinterpret_cast<const uint4*>(h8 + i * 256 + colq * 64);
-#pragma unroll
-        for (int c = 0; c < 8; ++c) q[c] = __ldg(p + c);
+        for (uint32_t c = 0; c < 4; ++c)
+          tma_bulk_g2s(base + kTOffAct + c * kKBlockBytes, src + c * kKBlockBytes, kKBlockBytes, bar_rows);
       }
-    };
-    if (pair_id < n_units) fetch(pair_id);
-    for (int64_t u = pair_id; u < n_units; u += n_pairs) {
-      const int64_t i = (2 * u + (int64_t)rank) * kTileM + row;
-      const bool valid = i < n;
-      int64_t g = 0;
-      float dir[3] = {0.f, 0.f, 0.f};
-      if (valid && colq < 2) {  // quarter 0 stores the colour at g, quarters 0 and 1 write PE4(dir)
-        g = (int64_t)__ldg(list + i);
-        const int64_t ray = g / S;
-        dir[0] = dirs[ray * 3 + 0];
-        dir[1] = dirs[ray * 3 + 1];
-        dir[2] = dirs[ray * 3 + 2];
-      }
-#pragma unroll
-      for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(kblock_row + swz[c]) = q[c];
-      if (colq == 0) write_pe16<kFp16, 0, kDirOctaves>(aux_row, r8, dir);
-      else if (colq == 1) write_pe16<kFp16, 16, kDirOctaves>(aux_row, r8, dir);
-      fence_proxy_async();
       __syncwarp();
-      if (elect_one()) mbar_arrive_cluster(bar_in, 0u);
-
-      // bottleneck, ActivationType::None: drained into the A tile it was computed from
-      mbar_wait(bar_acc, acc_par);
-      acc_par ^= 1u;
-      tc_fence_after();
-      float unused = 0.0f;
-      epi_cols<kFp16, false, false, true>(tr, taddr + (uint32_t)colq * 64u, C.bias[8] + colq * 64, C.w_alpha, unused,
-                                          kblock_row, swz);
+    };
+    auto fetch = [&](int64_t u) {
+      const int64_t i = (2 * u + (int64_t)rank) * kTileM + row;
+      meta_f = make_float4(0.f, 0.f, 0.f, 0.f);
+      valid_f = u < n_units && i < n;
+      if (valid_f && colq < 2) meta_f = __ldg(meta + i);  // quarter 0 stores the colour, quarters 0 and 1 write PE4(dir)
+    };
+    // PE4(dir) of the fetched unit -> aux buffer `b`; warp 0 also waits for the unit's rows; tells the issuer
+    auto stage = [&](uint32_t b) {
+      uint8_t* aux_row = smem + aux_row_off + b * kAuxBytes;
+      const float dir_f[3] = {meta_f.x, meta_f.y, meta_f.z};
+      if (colq == 0) write_pe16<kFp16, 0, kDirOctaves>(aux_row, r8, dir_f);
+      else if (colq == 1) write_pe16<kFp16, 16, kDirOctaves>(aux_row, r8, dir_f);
+      if (warp == 0) {
+        mbar_wait(bar_rows, rows_par);
+        rows_par ^= 1u;
+      }
       fence_proxy_async();
       tc_fence_before();
       __syncwarp();
-      if (elect_one()) mbar_arrive_cluster(bar_in, 0u);
-      // the next unit's rows: in flight during the viewdirs layer and the head (issued here, not earlier, so that the
-      // 32 registers do not overlap the 64 of the bottleneck drain)
-      if (u + n_pairs < n_units) fetch(u + n_pairs);
+      if (elect_one()) mbar_arrive_cluster(bar_in8, 0u);
+    };
+
+    int64_t g_cur = 0;
+    bool valid_cur = false;
+    if (pair_id < n_units) {
+      copy_rows(pair_id);
+      fetch(pair_id);
+      g_cur = (int64_t)__float_as_int(meta_f.w);
+      valid_cur = valid_f;
+      stage(0u);
+      fetch(pair_id + n_pairs);
+    }
+    for (int64_t u = pair_id; u < n_units; u += n_pairs) {
+      // bottleneck, ActivationType::None: accumulator + bias -> 16 bits -> tensor memory, 32 columns at a time
+      mbar_wait(bar_acc8, par);
+      tc_fence_after();
+#pragma unroll
+      for (int hb = 0; hb < 2; ++hb) {
+        uint32_t v[32], pk[16];
+        tc_ld32(taddr + (uint32_t)colq * 64u + 32u * hb, v);
+        tc_wait_ld();
+        const float* bias = C.bias[8] + colq * 64 + 32 * hb;
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          pk[j] = pack2<kFp16, false>(__uint_as_float(v[2 * j]) + bias[2 * j], __uint_as_float(v[2 * j + 1]) + bias[2 * j + 1]);
+        tc_st16(taddr + kTColA9 + (uint32_t)colq * 32u + 16u * hb, pk);
+      }
+      tc_wait_st();
+      tc_fence_before();
+      __syncwarp();
+      if (elect_one()) mbar_arrive_cluster(bar_in9, 0u);
+      // the A tile is free (the bottleneck MMAs have completed): the next unit's rows go in while viewdirs(u) runs
+      const bool more = u + n_pairs < n_units;
+      const int64_t g_next = (int64_t)__float_as_int(meta_f.w);
+      const bool valid_next = valid_f;
+      if (more) {
+        copy_rows(u + n_pairs);
+        stage(buf ^ 1u);
+        fetch(u + 2 * n_pairs);
+      }
 
       // viewdirs (ReLU) and the f32 rgb head: 32 columns per warp, as in the fused kernel
-      mbar_wait(bar_acc, acc_par);
-      acc_par ^= 1u;
+      mbar_wait(bar_acc9, par);
       tc_fence_after();
       uint32_t v[32];
       tc_ld32(taddr + 256u + 32u * (uint32_t)colq, v);
@@ -871,14 +916,14 @@ mlp_colour_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict_
       }
       tc_fence_before();
       if (colq != 0) {
-        float* scratch = reinterpret_cast<float*>(smem + kCOffAux + scratch_off);
+        float* scratch = reinterpret_cast<float*>(smem + scratch_off + buf * kAuxBytes);
         scratch[0] = r0;
         scratch[1] = r1;
         scratch[2] = r2;
       }
       named_bar_sync(row_bar, 128);
       if (colq == 0) {
-        const uint8_t* aux = smem + kCOffAux;
+        const uint8_t* aux = smem + kTOffAux + buf * kAuxBytes;
 #pragma unroll
         for (uint32_t k = 1; k < 4; ++k) {
           const float* sc = reinterpret_cast<const float*>(aux + sw128_offset(row, 32u + 8u * k));
@@ -886,13 +931,17 @@ mlp_colour_kernel(const __grid_constant__ TcConsts C, const uint8_t* __restrict_
           r1 += sc[1];
           r2 += sc[2];
         }
-        if (valid) {
-          rgb[g * 3 + 0] = 1.0f / (1.0f + expf(-r0));  // network.rs:165
-          rgb[g * 3 + 1] = 1.0f / (1.0f + expf(-r1));
-          rgb[g * 3 + 2] = 1.0f / (1.0f + expf(-r2));
+        if (valid_cur) {
+          rgb[g_cur * 3 + 0] = 1.0f / (1.0f + expf(-r0));  // network.rs:165
+          rgb[g_cur * 3 + 1] = 1.0f / (1.0f + expf(-r1));
+          rgb[g_cur * 3 + 2] = 1.0f / (1.0f + expf(-r2));
         }
       }
-      named_bar_sync(row_bar, 128);  // the scratch chunks are rewritten by the next unit
+      named_bar_sync(row_bar, 128);
+      g_cur = g_next;
+      valid_cur = valid_next;
+      par ^= 1u;
+      buf ^= 1u;
     }
   }
 
@@ -1025,7 +1074,7 @@ cudaError_t init_mlp_tc() {  // once per process and device, at context creation
     if (e != cudaSuccess) return e;
   }
   for (const void* k : {(const void*)mlp_colour_kernel<true>, (const void*)mlp_colour_kernel<false>}) {
-    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTSmemBytes);
     if (e != cudaSuccess) return e;
   }
   return cudaSuccess;
@@ -1060,7 +1109,7 @@ cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src_in, const Sam
   if (raw && (w.fmt != 1 || dst.rgb != nullptr)) return cudaErrorInvalidValue;  // only the fp16 density-only pass has it
   const bool skip = dst.skip_empty_rgb != 0 && dst.rgb != nullptr;
   const bool h8 = dst.h8 != nullptr;  // first phase of the two-phase fine pass
-  if (h8 && (raw || dst.rgb == nullptr || dst.h8_list == nullptr || dst.h8_count == nullptr || src.B > 0x7fffffff))
+  if (h8 && (raw || dst.rgb == nullptr || dst.h8_meta == nullptr || dst.h8_count == nullptr || src.B > 0x7fffffff))
     return cudaErrorInvalidValue;
   const int which = raw ? 0 : (h8 ? (w.fmt == 1 ? 5 : 6) : (w.fmt == 1 ? (skip ? 1 : 2) : (skip ? 3 : 4)));
   switch (which) {
@@ -1086,14 +1135,14 @@ cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src_in, const Sam
   return e;
 }
 
-cudaError_t launch_mlp_colour(const TcWeights& w, const uint16_t* d_h8, const int32_t* d_list, const uint32_t* d_count,
-                              const float* d_dirs, int S, float* d_rgb, int sm_count, cudaStream_t s) {
+cudaError_t launch_mlp_colour(const TcWeights& w, const uint16_t* d_h8, const float4* d_meta, const uint32_t* d_count,
+                              float* d_rgb, int sm_count, cudaStream_t s) {
   if (w.fmt != 0 && w.fmt != 1) return cudaErrorInvalidValue;
   const int grid = 2 * (sm_count / 2);  // the number of rows is on the device: a full persistent grid
   if (w.fmt == 1)
-    mlp_colour_kernel<true><<<grid, kColThreads, kCSmemBytes, s>>>(w.consts, w.d_chunks, d_h8, d_list, d_count, d_dirs, S, d_rgb);
+    mlp_colour_kernel<true><<<grid, kColThreads, kTSmemBytes, s>>>(w.consts, w.d_chunks, d_h8, d_meta, d_count, d_rgb);
   else
-    mlp_colour_kernel<false><<<grid, kColThreads, kCSmemBytes, s>>>(w.consts, w.d_chunks, d_h8, d_list, d_count, d_dirs, S, d_rgb);
+    mlp_colour_kernel<false><<<grid, kColThreads, kTSmemBytes, s>>>(w.consts, w.d_chunks, d_h8, d_meta, d_count, d_rgb);
   return cudaGetLastError();
 }
 

@@ -55,9 +55,9 @@ cudaError_t init_mlp_tc_tf32();
 cudaError_t launch_mlp_tc(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
                           cudaStream_t s);
 // Second phase of the two-phase fine pass: the colour branch over the *d_count rows of d_h8 that a
-// launch_mlp_tc with SampleDst::h8 stored; row i belongs to sample d_list[i] of ray d_list[i] / S, colour to d_rgb.
-cudaError_t launch_mlp_colour(const TcWeights& w, const uint16_t* d_h8, const int32_t* d_list, const uint32_t* d_count,
-                              const float* d_dirs, int S, float* d_rgb, int sm_count, cudaStream_t s);
+// launch_mlp_tc with SampleDst::h8 stored; d_meta[i] = {ray direction, sample id as bits} of row i, colour to d_rgb.
+cudaError_t launch_mlp_colour(const TcWeights& w, const uint16_t* d_h8, const float4* d_meta, const uint32_t* d_count,
+                              float* d_rgb, int sm_count, cudaStream_t s);
 cudaError_t launch_mlp_tc_x3(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
                              cudaStream_t s);
 cudaError_t launch_mlp_tc_tf32(const TcWeights& w, const SampleSrc& src, const SampleDst& dst, int sm_count,
