@@ -52,7 +52,7 @@ PRECISION_NOTE = {
 # the fine pass of the reference frame: 16 x mlp_tc_kernel<1,0,0,1> (0.55 GB read, 10.95 GB written: densities, zero colours
 # and the 512-byte rows of the 16 % of the samples that have density) + 16 x mlp_colour_kernel (10.17 GB read, 0.27 GB
 # written).  The fused single launch it replaced: 0.518 + 1.915 GB (profiles/r02_frame_ncu_full_summary.csv)
-NCU_FINE_DRAM_GB = 0.549 + 10.949 + 10.166 + 0.269
+NCU_FINE_DRAM_GB = 0.549 + 10.949 + 10.40 + 0.269
 NCU_FINE_DRAM_SOURCE = "profiles/r02_two_phase_ncu_full_summary.csv"
 
 

@@ -20,8 +20,8 @@
  *     on the device in the order they were enqueued (the next call's stream waits for an event the previous call
  *     recorded), so they never overlap; use one context per stream for concurrency.
  *   - Device memory of a context: the weights (15 MB in all operand formats) plus workspaces that grow with the
- *     largest call, about 5.3 KB per ray of a render chunk (1 Mi rays at most: NERF_B200_CHUNK_RAYS) - 3.4 GB for an
- *     800x800 frame - and, for renders in the 16-bit tensor-core modes, the hand-off buffer of the two-phase fine pass:
+ *     largest call, about 4.7 KB per ray of a render chunk at 64 + 128 samples (1 Mi rays at most: NERF_B200_CHUNK_RAYS) - 3.0 GB
+ *     for an 800x800 frame - and, for renders in the 16-bit tensor-core modes, the hand-off buffer of the two-phase fine pass:
  *     528 B per fine sample of a group of rays (40 960 rays x 192 samples = 4.2 GB; NERF_B200_FINE_SUB_RAYS sets the
  *     group, NERF_B200_TWO_PHASE=0 renders with one fused launch and no such buffer).
  */
