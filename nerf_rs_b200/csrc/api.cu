@@ -102,7 +102,7 @@ struct nerf_ctx {
   // sample has density.  Needs skip_empty (samples without density get rgb = 0) and a 16-bit tensor-core mode.
   bool two_phase_fine = true;
   int64_t fine_sub_rays = 40960;
-  DevBuf h8, h8_list, h8_count;
+  DevBuf h8, h8_meta, h8_count;
   float select_tau = 12.0f;     // NERF_B200_SELECT_TAU: optical depth behind which no coarse weight survives (T < 6e-6)
   // 8-bit output path: two device frames + two pinned host frames so that the copy of one view overlaps the next render
   DevBuf q8[2], depth, acc;
@@ -492,7 +492,7 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
       const TcWeights& wt = c->nets[NERF_NET_FINE].tc[precision == NERF_PREC_BF16 ? 0 : 1];
       const int64_t sub_max = std::min<int64_t>(nr, c->fine_sub_rays);
       // rows are stored as whole [128 x 256] tile images; a CTA pair of the colour kernel reads two tiles at a time
-      if ((rc = c->h8.reserve(((sub_max * nm + 255) / 256) * 256 * 512)) || (rc = c->h8_list.reserve(sub_max * nm * 16)) ||
+      if ((rc = c->h8.reserve(((sub_max * nm + 255) / 256) * 256 * 512)) || (rc = c->h8_meta.reserve(sub_max * nm * 16)) ||
           (rc = c->h8_count.reserve(256)))
         return rc;
       for (int64_t r0 = 0; r0 < nr && rc == NERF_OK; r0 += c->fine_sub_rays) {
@@ -506,7 +506,7 @@ int render_range(nerf_ctx* c, const nerf_camera& cam, int W, int H, int nc, int 
         d2.rgb = dst.rgb + r0 * nm * 3;
         d2.skip_empty_rgb = 0;
         d2.h8 = c->h8.as<uint16_t>();
-        d2.h8_meta = c->h8_list.as<float4>();
+        d2.h8_meta = c->h8_meta.as<float4>();
         d2.h8_count = c->h8_count.as<uint32_t>();
         NERF_CUDA(cudaMemsetAsync(d2.h8_count, 0, 4, s));
         rc = run_mlp(c, NERF_NET_FINE, s2, d2, precision, s);
@@ -742,7 +742,7 @@ void nerf_destroy(nerf_ctx* c) {
     }
     for (DevBuf* b : {&c->dirs, &c->tc, &c->sigc, &c->wc, &c->tf, &c->sigf, &c->rgbf, &c->out, &c->in_a, &c->in_b,
                       &c->jit, &c->uni, &c->q8[0], &c->q8[1], &c->depth, &c->acc, &c->sel_list, &c->sel_count, &c->alive[0], &c->alive[1],
-                      &c->ray_list, &c->ray_count, &c->dirs_alive, &c->h8, &c->h8_list, &c->h8_count})
+                      &c->ray_list, &c->ray_count, &c->dirs_alive, &c->h8, &c->h8_meta, &c->h8_count})
       b->release();
     if (c->h_ray_count) cudaFreeHost(c->h_ray_count);
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
