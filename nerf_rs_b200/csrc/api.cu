@@ -1067,12 +1067,13 @@ int nerf_render_rgb8(nerf_ctx* c, const nerf_camera* cam, int W, int H, int nc, 
     dev.u = c->uni.as<float>();
   }
   const size_t bytes = (size_t)n * channels;
-  if ((rc = c->q8[0].reserve(bytes)) || (rc = reserve_pinned(c, bytes))) return rc;
+  if ((rc = c->q8[0].reserve(bytes))) return rc;
   rc = nerf_render_rgb8_device(c, cam, W, H, nc, nf, precision, &dev, rb, re, channels, c->q8[0].as<uint8_t>(), s);
   if (rc != NERF_OK) return rc;
-  NERF_CUDA(cudaMemcpyAsync(c->pinned[0], c->q8[0].p, bytes, cudaMemcpyDeviceToHost, s));
+  // straight into the caller's buffer, as nerf_render does (a pinned or registered buffer is written by DMA; a pageable
+  // one goes through the driver's own staging - no second copy here)
+  NERF_CUDA(cudaMemcpyAsync(out, c->q8[0].p, bytes, cudaMemcpyDeviceToHost, s));
   NERF_CUDA(cudaStreamSynchronize(s));
-  std::memcpy(out, c->pinned[0], bytes);
   return NERF_OK;
 }
 
