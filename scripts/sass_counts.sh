@@ -7,7 +7,7 @@ cd "$(dirname "$0")/.."
 SO=nerf_rs_b200/libnerf_b200.so
 echo "# cuobjdump -sass $SO | grep -c <mnemonic>   ($(date -u +%Y-%m-%d), nvcc $(nvcc --version | grep -o 'V[0-9][0-9.]*' | tail -1))"
 cuobjdump -sass $SO > /tmp/_sass.txt
-for m in UTCHMMA UTCHMMA.2CTA LDTM UTCBAR UTCBAR.2CTA.MULTICAST UBLKCP.S.G UTMALDG SYNCS.ARRIVE.TRANS64 SYNCS.PHASECHK \
+for m in UTCHMMA UTCHMMA.2CTA LDTM STTM UTCBAR UTCBAR.2CTA.MULTICAST UBLKCP.S.G UTMALDG SYNCS.ARRIVE.TRANS64 SYNCS.PHASECHK \
          UTCATOMSWS HMMA WGMMA STL LDL; do
   printf "%-24s %s\n" "$m" "$(grep -c "[ .]$m[ .;]" /tmp/_sass.txt || true)"
 done
